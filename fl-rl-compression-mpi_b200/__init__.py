@@ -1,0 +1,145 @@
+"""Python binding of the B200-native FL/RL codec (ctypes over the C ABI in include/flrl.h).
+
+The directory name mirrors the reference repo and is not a Python identifier; import it with
+``importlib.import_module("fl-rl-compression-mpi_b200")`` (see ``flrl_import()`` in
+tests/conftest.py).  PyTorch is used only for device memory and streams.
+
+There is no CPU fallback: if ``libflrl.so`` is missing or fails to load, importing this
+module raises.  Build it with ``python -c "import __graft_entry__ as g; g.build()"`` or
+``make -C fl-rl-compression-mpi_b200``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libflrl.so")
+FRAME = 128
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(f"{LIB_PATH} not built — run `make -C {HERE}` (no CPU fallback exists)")
+lib = C.CDLL(LIB_PATH)
+
+_vp, _sz, _u8p = C.c_void_p, C.c_size_t, C.POINTER(C.c_uint8)
+
+lib.flrl_last_error.restype = C.c_char_p
+lib.flrl_version.restype = C.c_int
+lib.flrl_fl_frames.restype = _sz
+lib.flrl_fl_frames.argtypes = [_sz]
+lib.flrl_fl_workspace_bytes.restype = _sz
+lib.flrl_fl_workspace_bytes.argtypes = [_sz]
+lib.flrl_fl_encode.restype = C.c_int
+lib.flrl_fl_encode.argtypes = [_vp, _sz, _vp, _vp, _sz, _vp, _vp, _sz, _vp]
+lib.flrl_fl_decode.restype = C.c_int
+lib.flrl_fl_decode.argtypes = [_vp, _sz, _vp, _sz, _vp, _sz, _vp, _vp, _sz, _vp]
+
+
+class FlrlError(RuntimeError):
+    pass
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise FlrlError(f"{what}: rc={rc}: {lib.flrl_last_error().decode(errors='replace')}")
+
+
+def _torch():
+    import torch
+
+    if not torch.cuda.is_available():
+        raise FlrlError("CUDA device required: the fl / rl methods have no CPU fallback")
+    return torch
+
+
+def _stream_ptr(torch) -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t) -> int:
+    return t.data_ptr() if t.numel() else 0
+
+
+# ------------------------------------------------------------------ device layer: FL
+class FLEncoder:
+    """Reusable buffers for flrl_fl_encode over inputs of up to `n` bytes on the current device."""
+
+    def __init__(self, n: int):
+        torch = _torch()
+        self.n = n
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.bits = torch.empty(max(lib.flrl_fl_frames(n), 1), dtype=torch.uint8, device=dev)
+        self.cap = (n + 15) // 16 * 16
+        self.values = torch.empty(max(self.cap, 16), dtype=torch.uint8, device=dev)
+        self.size = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.ws_bytes = lib.flrl_fl_workspace_bytes(n)
+        self.ws = torch.empty(max(self.ws_bytes, 16), dtype=torch.uint8, device=dev)
+
+    def launch(self, d_in, n: int | None = None) -> None:
+        """Asynchronous on the current torch stream."""
+        torch = _torch()
+        n = d_in.numel() if n is None else n
+        assert n <= self.n and d_in.dtype == torch.uint8 and d_in.is_cuda
+        rc = lib.flrl_fl_encode(_ptr(d_in), n, _ptr(self.bits), _ptr(self.values), self.cap, _ptr(self.size), _ptr(self.ws),
+                                self.ws_bytes, _stream_ptr(torch))
+        _check(rc, "flrl_fl_encode")
+
+    def result(self, n: int):
+        """(bits, values) as device tensors (synchronises to read the size)."""
+        nv = int(self.size.item())
+        return self.bits[: lib.flrl_fl_frames(n)], self.values[:nv]
+
+
+class FLDecoder:
+    def __init__(self, n: int):
+        torch = _torch()
+        self.n = n
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.out = torch.empty(max((n + 15) // 16 * 16, 16), dtype=torch.uint8, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.ws_bytes = lib.flrl_fl_workspace_bytes(n)
+        self.ws = torch.empty(max(self.ws_bytes, 16), dtype=torch.uint8, device=dev)
+
+    def launch(self, d_bits, d_values, n: int) -> None:
+        torch = _torch()
+        assert n <= self.n
+        rc = lib.flrl_fl_decode(_ptr(d_bits), d_bits.numel(), _ptr(d_values), d_values.numel(), _ptr(self.out), n,
+                                _ptr(self.status), _ptr(self.ws), self.ws_bytes, _stream_ptr(torch))
+        _check(rc, "flrl_fl_decode")
+
+    def result(self, n: int):
+        st = int(self.status.item())
+        if st:
+            raise FlrlError(f"flrl_fl_decode: malformed container (status {st})")
+        return self.out[:n]
+
+
+def fl_encode_device(d_in):
+    """One-shot: uint8 CUDA tensor -> (bits, values) CUDA tensors."""
+    enc = FLEncoder(d_in.numel())
+    enc.launch(d_in)
+    return enc.result(d_in.numel())
+
+
+def fl_decode_device(d_bits, d_values, n: int):
+    dec = FLDecoder(n)
+    dec.launch(d_bits, d_values, n)
+    return dec.result(n)
+
+
+def _aligned_values(torch, v):
+    """Device copies of compressed arrays must be 16-byte aligned for the TMA bulk loads."""
+    t = torch.empty((v.numel() + 15) // 16 * 16 + 16, dtype=torch.uint8, device=v.device)
+    t[: v.numel()] = v
+    return t[: v.numel()]
+
+
+def to_device(a):
+    torch = _torch()
+    a = np.ascontiguousarray(np.frombuffer(a, dtype=np.uint8) if isinstance(a, (bytes, bytearray, memoryview)) else a)
+    t = torch.empty(max((a.size + 15) // 16 * 16, 16), dtype=torch.uint8, device="cuda")
+    if a.size:
+        t[: a.size] = torch.from_numpy(a.copy())
+    return t[: a.size]
