@@ -55,13 +55,16 @@ __device__ __forceinline__ uint32_t tile_scan_widths(TileScan& sc, int lane)
 // ---- final partial frame (len = n % 128 in 1..127), all THREADS threads participate --------
 // fl_cpu.cu:37-50 (width), :64-84 (packing), :53 (size = ceil(bits/8)).
 __device__ __noinline__ uint32_t encode_tail_frame(const uint8_t* in, uint32_t len, uint8_t* bits_out, uint8_t* vout,
-                                                   uint32_t* scratch /* >= 33 words smem */)
+                                                   uint32_t* scratch /* >= 35 words smem */)
 {
     const int tid = threadIdx.x;
     const uint32_t v = (tid < (int)len) ? in[tid] : 0u;
-    if (tid < 33) scratch[tid] = 0;
-    const uint32_t o = __syncthreads_or((int)v);
-    const uint32_t b = width_of_or(o);
+    if (tid < 35) scratch[tid] = 0;
+    __syncthreads();
+    const uint32_t wo = __reduce_or_sync(0xffffffffu, v);
+    if ((tid & 31) == 0 && wo) atomicOr(&scratch[34], wo);
+    __syncthreads();
+    const uint32_t b = width_of_or(scratch[34]);
     if (tid < (int)len) {
         const uint32_t bit = tid * b;
         const uint32_t w = bit >> 5, sh = bit & 31;
