@@ -16,6 +16,9 @@
 // final partial frame (n % 128 != 0) goes through a small cooperative scalar path in the
 // last tile, which also publishes the total value size.
 #include "fl_kernels.cuh"
+
+#include <stdlib.h>
+
 #include "flrl_bits.cuh"
 #include "lookback.cuh"
 
@@ -25,8 +28,25 @@ static constexpr int TILE_FRAMES = 128;
 static constexpr int TILE_BYTES = TILE_FRAMES * 128;  // 16 KiB
 static constexpr int THREADS = 128;
 static constexpr int ITEMS = 4;  // 32-byte items per thread per tile
+static constexpr long long FL_LEAD_TILES = 2048;  // distance between the two touches of a tile (32 MiB)
 
-struct TileScan {
+// Development trace (FLRL_TRACE builds only): per-tile globaltimer stamps.
+#ifdef FLRL_TRACE
+__device__ uint64_t* g_trace = nullptr;
+__device__ __forceinline__ void trace(long long tile, int slot)
+{
+    if (g_trace) {
+        uint64_t t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_trace[tile * 12 + slot] = t;
+    }
+}
+#define TRACE(tile, slot, cond) do { if (cond) trace(tile, slot); } while (0)
+#else
+#define TRACE(tile, slot, cond) do { } while (0)
+#endif
+
+struct __align__(16) TileScan {
     uint16_t off[TILE_FRAMES];  // exclusive prefix of widths inside the tile (16-byte units)
     uint8_t b[TILE_FRAMES];
     uint32_t total;
@@ -93,151 +113,280 @@ __device__ __noinline__ void decode_tail_frame(const uint8_t* vin, uint32_t avai
 // =============================================================================================
 //                                         ENCODE
 // =============================================================================================
-__global__ void __launch_bounds__(THREADS, 8)
-fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__ bits, uint8_t* __restrict__ values,
-                 uint64_t* __restrict__ values_size, uint64_t* __restrict__ desc)
+// Two touches per tile, `lead` tiles apart, in ONE kernel:
+//   CTA c  = width pass of tile c            (first touch: DRAM -> L2 -> smem; posts the tile's
+//                                             aggregate and writes its 128 widths)
+//          + pack  pass of tile c - lead     (second touch: an L2 hit; its own aggregate and those
+//                                             of all predecessors were posted `lead` CTAs ago, so
+//                                             the look-back never waits on a straggling load)
+// Why: the value offset of a tile needs the widths of every earlier tile.  In a classic
+// one-touch decoupled look-back the packed tile sits in shared memory until the slowest
+// earlier load has landed; measured on B200 that wait was 6.5 us of a 10 us CTA lifetime
+// and capped 1 GiB encode at 0.45 ms no matter how wide the look-back was.  `lead` (2048
+// tiles = 32 MiB) exceeds the ~1000 resident CTAs and stays far inside the 126 MB L2, so the
+// input is still read from DRAM once.
+//
+// CTA = 4 pack warps + 1 control warp.  Control: both TMA loads, look-back + inclusive
+// prefix at CTA start, TMA store.  Pack warps: pack tile c-lead in place, then widths of tile c.
+static constexpr int ENC_THREADS = THREADS + 32;
+static constexpr uint32_t BAR_OFFSETS = 2, BAR_PACKED = 3, BAR_PACKW_A = 4, BAR_PACKW_C = 6;
+
+// 16 width bytes -> 16 nibbles; frames at or past `valid` get the filler 0xf (never 0)
+__device__ __forceinline__ uint64_t nibbles_of_bytes(uint4 q, int valid)
 {
-    extern __shared__ __align__(128) uint8_t tile[];  // TILE_BYTES: input tile, then packed output in place
-    __shared__ __align__(8) uint64_t bar;
-    __shared__ TileScan sc;
-    __shared__ uint32_t tail_scratch[36];
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int t = tid & 3;  // quarter of the frame owned by this lane
-    const size_t full_frames = n / FRAME;
-    const long long tileno = blockIdx.x;
-    const size_t f0 = (size_t)tileno * TILE_FRAMES;
-    const int nfr = (int)(full_frames > f0 ? (full_frames - f0 < (size_t)TILE_FRAMES ? full_frames - f0 : TILE_FRAMES) : 0);
-
-    if (tid == 0) {
-        mbar_init(&bar, 1);
-        fence_mbar_init();
-        if (nfr) {
-            mbar_expect_tx(&bar, (uint32_t)nfr * FRAME);
-            tma_load_1d(tile, in + f0 * FRAME, (uint32_t)nfr * FRAME, &bar);
-        }
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+    uint64_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t b = (w[i >> 2] >> (8 * (i & 3))) & 0xf;
+        r |= (uint64_t)(i < valid ? b : 0xfu) << (4 * i);
     }
-    __syncthreads();
-    if (nfr) mbar_wait(&bar, 0);
+    return r;
+}
+__device__ __forceinline__ uint4 bytes_of_nibbles(uint64_t x, int valid)
+{
+    uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const uint32_t b = (uint32_t)(x >> (4 * i)) & 0xf;
+        w[i >> 2] |= (i < valid ? b : 0u) << (8 * (i & 3));
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
 
-    // ---- stage 1: items to registers, width per frame -------------------------------------
-    uint4 A[ITEMS], C[ITEMS];
-    uint32_t bw[ITEMS];
+__device__ __forceinline__ int tile_full_frames(size_t full_frames, size_t f0)
+{
+    return (int)(full_frames > f0 ? (full_frames - f0 < (size_t)TILE_FRAMES ? full_frames - f0 : TILE_FRAMES) : 0);
+}
+
+// widths of the 4 frame-quarters this lane owns in a staged tile; optionally keeps the data
+template <bool KEEP>
+__device__ __forceinline__ void lane_widths(const uint8_t* tile, int tid, int nfr, uint4 (&A)[ITEMS], uint4 (&C)[ITEMS],
+                                            uint32_t (&bw)[ITEMS], uint8_t* sb)
+{
+    const int t = tid & 3;
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
         const int fr = i * 32 + (tid >> 2);
-        uint32_t o = 0;
-        if (fr < nfr) {
-            const uint4* p = reinterpret_cast<const uint4*>(tile + fr * 128 + t * 32);
-            A[i] = p[0];
-            C[i] = p[1];
-            o = (A[i].x | A[i].y | A[i].z) | (A[i].w | C[i].x | C[i].y) | (C[i].z | C[i].w);
-        } else {
-            A[i] = make_uint4(0, 0, 0, 0);
-            C[i] = make_uint4(0, 0, 0, 0);
+        // unconditional: frames past nfr read stale shared memory and get width 0 (no stores)
+        const uint4* p = reinterpret_cast<const uint4*>(tile + fr * 128 + t * 32);
+        const uint4 a = p[0], c = p[1];
+        if (KEEP) {
+            A[i] = a;
+            C[i] = c;
         }
+        uint32_t o = (a.x | a.y | a.z) | (a.w | c.x | c.y) | (c.z | c.w);
         o |= __shfl_xor_sync(0xffffffffu, o, 1);
         o |= __shfl_xor_sync(0xffffffffu, o, 2);
         o |= o >> 16;
         o |= o >> 8;
         const uint32_t b = (fr < nfr) ? width_of_or(o) : 0u;
         bw[i] = b;
-        if (t == 0) sc.b[fr] = (uint8_t)b;
+        if (t == 0) sb[fr] = (uint8_t)b;
+    }
+}
+
+__global__ void __launch_bounds__(ENC_THREADS, 6)
+fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__ bits, uint8_t* __restrict__ values,
+                 uint64_t* __restrict__ values_size, uint64_t* __restrict__ desc, uint64_t* __restrict__ wdesc,
+                 long long tiles, long long lead)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* tileP = smem;               // pack pass: input tile, then packed output in place
+    uint8_t* tileW = smem + TILE_BYTES;  // width pass
+    __shared__ __align__(8) uint64_t barP, barW;
+    __shared__ TileScan sc;
+    __shared__ __align__(16) uint8_t wb[TILE_FRAMES];
+    __shared__ __align__(16) uint4 ktab[9];  // PackK{k1,k2,k3,ra} per width
+    __shared__ uint32_t tail_scratch[36];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t full_frames = n / FRAME;
+    const long long cw = blockIdx.x;         // tile of the width pass (valid if < tiles)
+    const long long cp = cw - lead;          // tile of the pack pass  (valid if >= 0)
+    const bool doW = cw < tiles, doP = cp >= 0;
+    const size_t fW = (size_t)cw * TILE_FRAMES, fP = doP ? (size_t)cp * TILE_FRAMES : 0;
+    const int nfrW = doW ? tile_full_frames(full_frames, fW) : 0;
+    const int nfrP = doP ? tile_full_frames(full_frames, fP) : 0;
+    const bool lastP = doP && cp == tiles - 1;
+
+    if (tid == THREADS) {
+        TRACE(cw, 0, true);
+        mbar_init(&barP, 1);
+        mbar_init(&barW, 1);
+        fence_mbar_init();
+        if (nfrP) {  // second touch: L2 hit, not needed afterwards
+            mbar_expect_tx(&barP, (uint32_t)nfrP * FRAME);
+            tma_load_1d_hint(tileP, in + fP * FRAME, (uint32_t)nfrP * FRAME, &barP, l2_policy_evict_first());
+        }
+        if (nfrW) {  // first touch: from DRAM, keep in L2 for the pack pass `lead` CTAs later
+            mbar_expect_tx(&barW, (uint32_t)nfrW * FRAME);
+            tma_load_1d_hint(tileW, in + fW * FRAME, (uint32_t)nfrW * FRAME, &barW, l2_policy_evict_last());
+        }
+    }
+    if (tid <= 8) {
+        const PackK k = make_pack_k(tid ? tid : 8);
+        ktab[tid] = tid ? make_uint4(k.k1, k.k2, k.k3, k.ra) : make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
 
-    // ---- stage 2: widths out, in-tile scan, publish aggregate -----------------------------
-    if (tid < nfr) bits[f0 + tid] = sc.b[tid];
-    if (warp == 0) {
-        const uint32_t total = tile_scan_widths(sc, lane);
-        if (lane == 0) {
-            sc.total = total;
-            st_relaxed_u64(desc + tileno, (tileno == 0 ? LB_INC : LB_AGG) | total);
-        }
-    }
-    __syncthreads();  // also: every thread's reads of the staged tile are complete -> in-place writes are safe
-
-    // ---- stage 3: pack in place ------------------------------------------------------------
-    uint32_t* tw = reinterpret_cast<uint32_t*>(tile);
+    if (warp < 4) {
+        // =============================== pack warps ========================================
+        uint4 A[ITEMS], C[ITEMS];
+        uint32_t bw[ITEMS];
+        if (doP) {
+            const int t = tid & 3;
+            bar_sync(BAR_OFFSETS, ENC_THREADS);  // control warp: sc.b (widths from the width pass) and sc.off
+            if (nfrP) mbar_wait(&barP, 0);
+            TRACE(cw, 1, tid == 0);
 #pragma unroll
-    for (int i = 0; i < ITEMS; ++i) {
-        const int fr = i * 32 + (tid >> 2);
-        if (fr < nfr) {
-            const uint32_t b = bw[i];
-            const PackK k = make_pack_k(b);
-            uint32_t* w = tw + (uint32_t)sc.off[fr] * 4u + b * t;
-            const uint32_t a[4] = {A[i].x, A[i].y, A[i].z, A[i].w};
-            const uint32_t c[4] = {C[i].x, C[i].y, C[i].z, C[i].w};
-            pack32_store(a, c, b, k, [&](uint32_t j, uint32_t v) { w[j] = v; });
+            for (int i = 0; i < ITEMS; ++i) {
+                const int fr = i * 32 + (tid >> 2);
+                const uint4* p = reinterpret_cast<const uint4*>(tileP + fr * 128 + t * 32);
+                A[i] = p[0];
+                C[i] = p[1];
+                bw[i] = sc.b[fr];
+            }
+            bar_sync(BAR_PACKW_A, THREADS);  // every read of the staged tile is done: pack in place
+            TRACE(cw, 2, tid == 0);
+            const uint32_t tw = smem_u32(tileP);
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i) {
+                const int fr = i * 32 + (tid >> 2);
+                const uint32_t b = bw[i];  // 0 for frames past nfr: every store below is predicated off
+                const uint4 kk = ktab[b];
+                PackK k;
+                k.k1 = kk.x; k.k2 = kk.y; k.k3 = kk.z; k.ra = kk.w; k.s8 = 8 * b;
+                const uint32_t w = tw + ((uint32_t)sc.off[fr] * 4u + b * t) * 4u;
+                const uint32_t a[4] = {A[i].x, A[i].y, A[i].z, A[i].w};
+                const uint32_t c[4] = {C[i].x, C[i].y, C[i].z, C[i].w};
+                pack32_store(a, c, b, k, [&](bool p, uint32_t j, uint32_t v) { sts32_pred(w + 4u * j, v, p); });
+            }
+            fence_proxy_async_smem();
+            TRACE(cw, 5, tid == 0);
+            bar_arrive(BAR_PACKED, ENC_THREADS);
+        }
+        if (doW) {
+            if (nfrW) mbar_wait(&barW, 0);
+            TRACE(cw, 3, tid == 0);
+            lane_widths<false>(tileW, tid, nfrW, A, C, bw, wb);
+            bar_sync(BAR_PACKW_C, THREADS);
+            if (warp == 0) {
+                const uint32_t v = reinterpret_cast<const uint32_t*>(wb)[lane];
+                uint32_t s = (v & 0xff) + ((v >> 8) & 0xff) + ((v >> 16) & 0xff) + (v >> 24);
+                s = __reduce_add_sync(0xffffffffu, s);
+                if (nfrW == TILE_FRAMES && (reinterpret_cast<uintptr_t>(bits) & 3) == 0) {
+                    reinterpret_cast<uint32_t*>(bits + fW)[lane] = v;
+                } else {
+                    for (int f = lane; f < nfrW; f += 32) bits[fW + f] = wb[f];
+                }
+                // hand the widths to the pack pass of this tile: 16 nibbles per word, each word
+                // self-validating (a width is never 0), so relaxed stores/loads suffice — no fences
+                if (lane < 8) {
+                    const uint4 q = reinterpret_cast<const uint4*>(wb)[lane];
+                    st_relaxed_u64(wdesc + cw * 8 + lane, nibbles_of_bytes(q, nfrW - 16 * lane));
+                }
+                if (lane == 0) st_relaxed_u64(desc + cw, LB_AGG | s);
+            }
+            TRACE(cw, 4, tid == 0);
+        }
+        if (!lastP) return;
+    } else {
+        // =============================== control warp ======================================
+        if (!doP) return;
+        // widths of tile cp were published by CTA cp's width pass `lead` CTAs ago
+        if (lane < 8) {
+            uint64_t w;
+            do { w = ld_relaxed_u64(wdesc + cp * 8 + lane); } while (w == 0);
+            reinterpret_cast<uint4*>(sc.b)[lane] = bytes_of_nibbles(w, nfrP - 16 * lane);
+        }
+        __syncwarp();
+        const uint32_t total = tile_scan_widths(sc, lane);
+        if (lane == 0) sc.total = total;
+        __syncwarp();
+        bar_arrive(BAR_OFFSETS, ENC_THREADS);
+        const uint64_t excl = lookback_exclusive_sum(desc, cp, lane);
+        if (lane == 0) st_relaxed_u64(desc + cp, LB_INC | (excl + total));
+        TRACE(cw, 6, lane == 0);
+        bar_sync(BAR_PACKED, ENC_THREADS);
+        if (lane == 0) {
+            if (total) {
+                tma_store_1d_hint(values + excl * 16, tileP, total * 16, l2_policy_evict_first());
+                tma_store_commit();
+            }
+            sc.base = excl;
+        }
+        if (!lastP) {
+            if (lane == 0) tma_store_wait_read<0>();  // smem must outlive the bulk store's reads
+            TRACE(cw, 7, lane == 0);
+            return;
         }
     }
-    fence_proxy_async_smem();
-
-    // ---- stage 4: look-back, then one bulk store -------------------------------------------
-    if (warp == 0) {
-        uint64_t excl = 0;
-        if (tileno > 0) {
-            excl = lookback_exclusive_sum(desc, tileno, lane);
-            if (lane == 0) st_relaxed_u64(desc + tileno, LB_INC | (excl + sc.total));
-        }
-        if (lane == 0) sc.base = excl;
-    }
+    // ---- CTA of the last tile only: the partial frame and the total size ----------------------
     __syncthreads();
-    const uint32_t total = sc.total;
-    const uint64_t base = sc.base;
-    if (tid == 0 && total) {
-        tma_store_1d(values + base * 16, tile, total * 16);
-        tma_store_commit();
-    }
-    if (tileno == (long long)gridDim.x - 1) {
+    {
         const uint32_t tail = (uint32_t)(n % FRAME);
-        uint64_t vsize = (base + total) * 16;
+        uint64_t vsize = (sc.base + sc.total) * 16;
         if (tail) {
             vsize += encode_tail_frame(in + full_frames * FRAME, tail, bits + full_frames, values + vsize, tail_scratch);
         }
         if (tid == 0) *values_size = vsize;
     }
-    if (tid == 0) tma_store_wait_read<0>();  // smem must outlive the bulk store's reads
+    if (tid == THREADS) tma_store_wait_read<0>();
 }
 
 // =============================================================================================
 //                                         DECODE
 // =============================================================================================
-__global__ void __launch_bounds__(THREADS, 6)
+// Same CTA shape: the control warp reads the tile's 128 widths (one word per lane), scans,
+// walks the look-back, and issues the TMA load of exactly the tile's value bytes; the four
+// unpack warps wait on the mbarrier, unpack into the output staging buffer, and the control
+// warp issues the TMA store.
+__global__ void __launch_bounds__(ENC_THREADS, 6)
 fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t* __restrict__ values, size_t nvalues,
                  uint8_t* __restrict__ out, size_t n, uint64_t* __restrict__ desc, int* __restrict__ err)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* vin = smem;                     // TILE_BYTES + 64 (slack for the unpacker's over-reads)
+    uint8_t* vin = smem;                      // TILE_BYTES + 128 (slack for the unpacker's over-reads)
     uint8_t* vout = smem + TILE_BYTES + 128;  // TILE_BYTES
     __shared__ __align__(8) uint64_t bar;
     __shared__ TileScan sc;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int t = tid & 3;
     const size_t full_frames = n / FRAME;
     const long long tileno = blockIdx.x;
     const size_t f0 = (size_t)tileno * TILE_FRAMES;
     const int nfr = (int)(full_frames > f0 ? (full_frames - f0 < (size_t)TILE_FRAMES ? full_frames - f0 : TILE_FRAMES) : 0);
+    const bool last = tileno == (long long)gridDim.x - 1;
 
-    if (tid == 0) {
+    if (tid == THREADS) {
         mbar_init(&bar, 1);
         fence_mbar_init();
     }
-    {
-        uint32_t b = 0;
-        if (tid < nfr) {
-            b = bits[f0 + tid];
-            if (b > 8u || b == 0u) {  // malformed container: never index out of range
-                atomicExch(err, 1);
-                b = b ? 8u : 0u;
-            }
-        }
-        sc.b[tid] = (uint8_t)b;
-    }
     __syncthreads();
 
-    if (warp == 0) {
+    if (warp == 4) {
+        // =============================== control warp ======================================
+        uint32_t w4 = 0;
+        if (nfr == TILE_FRAMES && (reinterpret_cast<uintptr_t>(bits) & 3) == 0) {
+            w4 = reinterpret_cast<const uint32_t*>(bits + f0)[lane];
+        } else {
+            for (int k = 0; k < 4; ++k) {
+                const int f = lane * 4 + k;
+                if (f < nfr) w4 |= (uint32_t)bits[f0 + f] << (8 * k);
+            }
+        }
+        // malformed container: widths must be 1..8 (never index out of range)
+        bool bad = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t b = (w4 >> (8 * k)) & 0xff;
+            if (lane * 4 + k < nfr && (b == 0 || b > 8)) bad = true;
+            if (b > 8) w4 = (w4 & ~(0xffu << (8 * k))) | (8u << (8 * k));
+        }
+        if (bad) atomicExch(err, 1);
+        reinterpret_cast<uint32_t*>(sc.b)[lane] = w4;
+        __syncwarp();
         uint32_t total = tile_scan_widths(sc, lane);
         uint64_t excl = 0;
         if (tileno > 0) {
@@ -257,35 +406,47 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
                 tma_load_1d(vin, values + excl * 16, total * 16, &bar);
             }
         }
-    }
-    __syncthreads();
-    const uint32_t total = sc.total;
-    if (total) {
-        mbar_wait(&bar, 0);
-        const uint32_t* vw = reinterpret_cast<const uint32_t*>(vin);
-#pragma unroll
-        for (int i = 0; i < ITEMS; ++i) {
-            const int fr = i * 32 + (tid >> 2);
-            if (fr < nfr) {
-                const uint32_t b = sc.b[fr];
-                const UnpackK k = make_unpack_k(b ? b : 1u);
-                const uint32_t* w = vw + (uint32_t)sc.off[fr] * 4u + b * t;
-                uint32_t a[4], c[4];
-                unpack32_load(b, k, [&](uint32_t j) { return w[j]; }, a, c);
-                if (b == 0) { a[0] = a[1] = a[2] = a[3] = 0; c[0] = c[1] = c[2] = c[3] = 0; }
-                uint4* o = reinterpret_cast<uint4*>(vout + fr * 128 + t * 32);
-                o[0] = make_uint4(a[0], a[1], a[2], a[3]);
-                o[1] = make_uint4(c[0], c[1], c[2], c[3]);
-            }
+        __syncwarp();
+        bar_arrive(BAR_OFFSETS, ENC_THREADS);
+        bar_sync(BAR_PACKED, ENC_THREADS);
+        if (lane == 0 && sc.total && nfr) {
+            tma_store_1d(out + f0 * FRAME, vout, (uint32_t)nfr * FRAME);
+            tma_store_commit();
         }
-        fence_proxy_async_smem();
+        if (!last) {
+            if (lane == 0) tma_store_wait_read<0>();
+            return;
+        }
+    } else {
+        // =============================== unpack warps ======================================
+        const int t = tid & 3;
+        bar_sync(BAR_OFFSETS, ENC_THREADS);
+        if (sc.total) {
+            mbar_wait(&bar, 0);
+            const uint32_t* vw = reinterpret_cast<const uint32_t*>(vin);
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i) {
+                const int fr = i * 32 + (tid >> 2);
+                if (fr < nfr) {
+                    const uint32_t b = sc.b[fr];
+                    const UnpackK k = make_unpack_k(b ? b : 1u);
+                    const uint32_t* w = vw + (uint32_t)sc.off[fr] * 4u + b * t;
+                    uint32_t a[4], c[4];
+                    unpack32_load(b, k, [&](uint32_t j) { return w[j]; }, a, c);
+                    if (b == 0) { a[0] = a[1] = a[2] = a[3] = 0; c[0] = c[1] = c[2] = c[3] = 0; }
+                    uint4* o = reinterpret_cast<uint4*>(vout + fr * 128 + t * 32);
+                    o[0] = make_uint4(a[0], a[1], a[2], a[3]);
+                    o[1] = make_uint4(c[0], c[1], c[2], c[3]);
+                }
+            }
+            fence_proxy_async_smem();
+        }
+        bar_arrive(BAR_PACKED, ENC_THREADS);
+        if (!last) return;
     }
+    // ---- last tile only: the partial frame ---------------------------------------------------
     __syncthreads();
-    if (tid == 0 && total && nfr) {
-        tma_store_1d(out + f0 * FRAME, vout, (uint32_t)nfr * FRAME);
-        tma_store_commit();
-    }
-    if (tileno == (long long)gridDim.x - 1) {
+    {
         const uint32_t tail = (uint32_t)(n % FRAME);
         if (tail && nframes == full_frames + 1) {
             const uint64_t off = (sc.base + sc.total) * 16;
@@ -298,7 +459,7 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
             }
         }
     }
-    if (tid == 0) tma_store_wait_read<0>();
+    if (tid == THREADS) tma_store_wait_read<0>();
 }
 
 // =============================================================================================
@@ -309,7 +470,16 @@ size_t fl_tiles(size_t n)
     const size_t frames = (n + FRAME - 1) / FRAME;
     return (frames + TILE_FRAMES - 1) / TILE_FRAMES;
 }
-size_t fl_workspace_bytes(size_t n) { return (fl_tiles(n) + 1) * sizeof(uint64_t) + 16; }
+// look-back descriptors (1 word/tile) + published widths (8 words/tile, encode) + status
+size_t fl_workspace_bytes(size_t n) { return (9 * fl_tiles(n) + 4) * sizeof(uint64_t) + 16; }
+
+#ifdef FLRL_TRACE
+extern "C" int flrl_debug_set_trace(void* d_buf)
+{
+    uint64_t* p = static_cast<uint64_t*>(d_buf);
+    return (int)cudaMemcpyToSymbol(g_trace, &p, sizeof p);
+}
+#endif
 
 const int* fl_decode_status(const void* d_ws, size_t n)
 {
@@ -333,9 +503,17 @@ cudaError_t fl_encode_launch(const uint8_t* d_in, size_t n, uint8_t* d_bits, uin
 {
     const size_t tiles = fl_tiles(n);
     uint64_t* desc = reinterpret_cast<uint64_t*>(d_ws);
-    cudaError_t e = cudaMemsetAsync(desc, 0, tiles * sizeof(uint64_t), stream);
+    uint64_t* wdesc = desc + ((tiles + 1) & ~(size_t)1);
+    cudaError_t e = cudaMemsetAsync(desc, 0, (((tiles + 1) & ~(size_t)1) + 8 * tiles) * sizeof(uint64_t), stream);
     if (e != cudaSuccess) return e;
-    fl_encode_kernel<<<(unsigned)tiles, THREADS, TILE_BYTES, stream>>>(d_in, n, d_bits, d_values, d_values_size, desc);
+    static const long long lead_cfg = getenv("FLRL_FL_LEAD") ? atoll(getenv("FLRL_FL_LEAD")) : FL_LEAD_TILES;
+    const long long lead = lead_cfg < (long long)tiles ? lead_cfg : (long long)tiles;
+    constexpr int smem = 2 * TILE_BYTES;
+    static bool done[64];
+    e = set_smem_once((const void*)fl_encode_kernel, smem, done);
+    if (e != cudaSuccess) return e;
+    fl_encode_kernel<<<(unsigned)(tiles + lead), ENC_THREADS, smem, stream>>>(d_in, n, d_bits, d_values, d_values_size, desc,
+                                                                              wdesc, (long long)tiles, lead);
     return cudaGetLastError();
 }
 
@@ -351,7 +529,7 @@ cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_
     static bool done[64];
     e = set_smem_once((const void*)fl_decode_kernel, smem, done);
     if (e != cudaSuccess) return e;
-    fl_decode_kernel<<<(unsigned)tiles, THREADS, smem, stream>>>(d_bits, nframes, d_values, nvalues, d_out, n, desc, err);
+    fl_decode_kernel<<<(unsigned)tiles, ENC_THREADS, smem, stream>>>(d_bits, nframes, d_values, nvalues, d_out, n, desc, err);
     return cudaGetLastError();
 }
 

@@ -116,6 +116,18 @@ FLRL_HD PackK make_pack_k(uint32_t b)
     return k;
 }
 
+// octet = (c1:c0) + c0 * k3 : one IMAD.WIDE.U32 whose addend is the register pair (c0, c1)
+FLRL_HD uint64_t pack_octet(uint32_t c0, uint32_t c1, uint32_t k3)
+{
+#if defined(__CUDA_ARCH__)
+    uint64_t r;
+    asm("{\n\t.reg .b64 t;\n\tmov.b64 t, {%1, %2};\n\tmad.wide.u32 %0, %1, %3, t;\n\t}" : "=l"(r) : "r"(c0), "r"(c1), "r"(k3));
+    return r;
+#else
+    return (((uint64_t)c1 << 32) | c0) + (uint64_t)c0 * k3;
+#endif
+}
+
 // 16 input bytes (x[0..3], little endian) of width b -> 16b bits, right aligned in (lo,hi).
 //   stage 1: t  = x + (x & 0x00ff00ff) * k1   -> pair (v0 + v1<<b) at bits [8-b, 8+b) of each half
 //   stage 2: c  = t + (t & 0x0000ffff) * k2   -> quad at bits [24-3b, 24+b)
@@ -131,18 +143,17 @@ FLRL_HD void pack16(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, const Pa
     uint32_t c1 = t1 + (t1 & 0xffffu) * k.k2;
     uint32_t c2 = t2 + (t2 & 0xffffu) * k.k2;
     uint32_t c3 = t3 + (t3 & 0xffffu) * k.k2;
-    uint64_t w0 = (((uint64_t)c1 << 32) | c0) + (uint64_t)c0 * k.k3;
-    uint64_t w1 = (((uint64_t)c3 << 32) | c2) + (uint64_t)c2 * k.k3;
-    uint64_t p0 = w0 >> k.ra;
-    uint64_t p1 = w1 >> k.ra;
+    uint64_t p0 = pack_octet(c0, c1, k.k3) >> k.ra;
+    uint64_t p1 = pack_octet(c2, c3, k.k3) >> k.ra;
     qlo = p0 | shl64c(p1, k.s8);
     qhi = p1 >> (64 - k.s8);
 }
 
 // 32 input bytes (two uint4: a = elements 0..15, c = 16..31 of this lane) -> b output words
-// stored at w[0..b).  `w` is the lane's word pointer: frame_word_base + b * t.
-// Q0 (first 16b bits) supplies words [0, b/2); the word at b/2 is shared when b is odd:
-// Q1 is shifted up 16 bits by a PRMT whose selector depends on the parity of b.
+// handed to st(pred, j, word) for j in [0, b): word j of the lane (frame_word_base + b*t + j).
+// Q0 (first 16b bits) supplies words [0, b/2); when b is odd the word at b/2 is shared: its low
+// half is the top 16 bits of Q0 and Q1 moves up 16 bits — both done by PRMTs whose selector
+// depends on the parity of b.  All eight stores are issued predicated, no branches.
 template <typename Store>
 FLRL_HD void pack32_store(const uint32_t a[4], const uint32_t c[4], uint32_t b, const PackK& k, Store&& st)
 {
@@ -152,22 +163,25 @@ FLRL_HD void pack32_store(const uint32_t a[4], const uint32_t c[4], uint32_t b, 
     const uint32_t A0 = (uint32_t)q0lo, A1 = (uint32_t)(q0lo >> 32), A2 = (uint32_t)q0hi, A3 = (uint32_t)(q0hi >> 32);
     const uint32_t C0 = (uint32_t)q1lo, C1 = (uint32_t)(q1lo >> 32), C2 = (uint32_t)q1hi, C3 = (uint32_t)(q1hi >> 32);
     const uint32_t q = b >> 1;
-    const uint32_t sel = (b & 1u) ? 0x5432u : 0x7654u;
-    // word q of Q0: the 16 straddling bits when b is odd, 0 when b is even (Q0 holds exactly 32q bits)
-    uint32_t aq = (q == 0) ? A0 : (q == 1) ? A1 : (q == 2) ? A2 : (q == 3) ? A3 : 0u;
-    uint32_t F0 = prmt(0u, C0, sel) | aq;
-    uint32_t F1 = prmt(C0, C1, sel);
-    uint32_t F2 = prmt(C1, C2, sel);
-    uint32_t F3 = prmt(C2, C3, sel);
+    const bool odd = (b & 1u) != 0;
+    const uint32_t sel = odd ? 0x5432u : 0x7654u;
+    const uint32_t sel0 = odd ? 0x5410u : 0x7654u;  // even b: F0 = C0, the pick below is ignored
+    const uint32_t a01 = (q & 1u) ? A1 : A0;
+    const uint32_t a23 = (q & 1u) ? A3 : A2;
+    const uint32_t aq = (q & 2u) ? a23 : a01;       // word floor(b/2) of Q0 (b odd, q <= 3)
+    const uint32_t F0 = prmt(aq, C0, sel0);
+    const uint32_t F1 = prmt(C0, C1, sel);
+    const uint32_t F2 = prmt(C1, C2, sel);
+    const uint32_t F3 = prmt(C2, C3, sel);
     const uint32_t nf = b - q;  // ceil(b/2) words come from F
-    if (0 < q) st(0u, A0);
-    if (1 < q) st(1u, A1);
-    if (2 < q) st(2u, A2);
-    if (3 < q) st(3u, A3);
-    st(q, F0);  // b >= 1 so nf >= 1
-    if (1 < nf) st(q + 1, F1);
-    if (2 < nf) st(q + 2, F2);
-    if (3 < nf) st(q + 3, F3);
+    st(0 < q, 0u, A0);
+    st(1 < q, 1u, A1);
+    st(2 < q, 2u, A2);
+    st(3 < q, 3u, A3);
+    st(b != 0, q, F0);  // b == 0 marks "no frame here" (tile tail): nothing is stored
+    st(1 < nf, q + 1, F1);
+    st(2 < nf, q + 2, F2);
+    st(3 < nf, q + 3, F3);
 }
 
 // ---- decode -----------------------------------------------------------------------------

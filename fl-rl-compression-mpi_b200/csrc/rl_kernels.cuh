@@ -1,0 +1,21 @@
+// rl_kernels.cuh — launchers of the run-length kernels (rl_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace flrl {
+
+size_t rl_encode_tiles(size_t n);
+size_t rl_encode_workspace_bytes(size_t n);
+size_t rl_decode_tiles(size_t pairs);
+size_t rl_decode_workspace_bytes(size_t pairs);
+
+// d_in, d_counts, d_values 16-byte aligned.  See include/flrl.h for the shard semantics.
+cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint64_t prev_run, uint8_t* d_counts,
+                             uint8_t* d_values, size_t pair_cap, uint64_t* d_pairs, void* d_ws, cudaStream_t stream);
+cudaError_t rl_decode_launch(const uint8_t* d_counts, const uint8_t* d_values, size_t pairs, uint8_t* d_out, size_t out_cap,
+                             uint64_t* d_out_size, void* d_ws, cudaStream_t stream);
+const int* rl_decode_status(const void* d_ws, size_t pairs);
+
+}  // namespace flrl

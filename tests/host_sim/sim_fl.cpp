@@ -28,7 +28,7 @@ uint64_t sim_fl_encode(const uint8_t* in, size_t n, uint8_t* bits, uint8_t* valu
             memcpy(a, in + f * 128 + t * 32, 16);
             memcpy(c, in + f * 128 + t * 32 + 16, 16);
             uint32_t* w = wbase + b * t;
-            pack32_store(a, c, b, k, [&](uint32_t j, uint32_t v) { w[j] = v; });
+            pack32_store(a, c, b, k, [&](bool p, uint32_t j, uint32_t v) { if (p) w[j] = v; });
         }
         off16 += b;
     }
