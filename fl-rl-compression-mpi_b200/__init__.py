@@ -143,3 +143,80 @@ def to_device(a):
     if a.size:
         t[: a.size] = torch.from_numpy(a.copy())
     return t[: a.size]
+
+
+# ------------------------------------------------------------------ device layer: RL
+lib.flrl_rl_workspace_bytes.restype = _sz
+lib.flrl_rl_workspace_bytes.argtypes = [_sz]
+lib.flrl_rl_decode_workspace_bytes.restype = _sz
+lib.flrl_rl_decode_workspace_bytes.argtypes = [_sz]
+lib.flrl_rl_encode.restype = C.c_int
+lib.flrl_rl_encode.argtypes = [_vp, _sz, _sz, C.c_uint64, _vp, _vp, _sz, _vp, _vp, _sz, _vp]
+lib.flrl_rl_decode.restype = C.c_int
+lib.flrl_rl_decode.argtypes = [_vp, _vp, _sz, _vp, _sz, _vp, _vp, _vp, _sz, _vp]
+
+
+class RLEncoder:
+    """Reusable buffers for flrl_rl_encode over shards of up to `n` bytes on the current device."""
+
+    def __init__(self, n: int):
+        torch = _torch()
+        self.n = n
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.cap = max((n + 15) // 16 * 16, 16)
+        self.counts = torch.empty(self.cap, dtype=torch.uint8, device=dev)
+        self.values = torch.empty(self.cap, dtype=torch.uint8, device=dev)
+        self.size = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.ws_bytes = lib.flrl_rl_workspace_bytes(n)
+        self.ws = torch.empty(max(self.ws_bytes, 16), dtype=torch.uint8, device=dev)
+
+    def launch(self, d_in, n: int | None = None, prev_run: int = 0) -> None:
+        """Encode d_in[:n]; bytes d_in[n:] are look-ahead only (shard semantics of include/flrl.h)."""
+        torch = _torch()
+        n_avail = d_in.numel()
+        n = n_avail if n is None else n
+        assert n <= self.n and d_in.dtype == torch.uint8 and d_in.is_cuda
+        rc = lib.flrl_rl_encode(_ptr(d_in), n, n_avail, prev_run, _ptr(self.counts), _ptr(self.values), self.cap,
+                                _ptr(self.size), _ptr(self.ws), self.ws_bytes, _stream_ptr(torch))
+        _check(rc, "flrl_rl_encode")
+
+    def result(self):
+        p = int(self.size.item())
+        return self.counts[:p], self.values[:p]
+
+
+class RLDecoder:
+    def __init__(self, out_cap: int, max_pairs: int | None = None):
+        torch = _torch()
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.out_cap = out_cap
+        self.out = torch.empty(max((out_cap + 15) // 16 * 16, 16), dtype=torch.uint8, device=dev)
+        self.size = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.ws_bytes = lib.flrl_rl_decode_workspace_bytes(out_cap if max_pairs is None else max_pairs)
+        self.ws = torch.empty(max(self.ws_bytes, 16), dtype=torch.uint8, device=dev)
+
+    def launch(self, d_counts, d_values) -> None:
+        torch = _torch()
+        assert d_counts.numel() == d_values.numel()
+        rc = lib.flrl_rl_decode(_ptr(d_counts), _ptr(d_values), d_counts.numel(), _ptr(self.out), self.out_cap, _ptr(self.size),
+                                _ptr(self.status), _ptr(self.ws), self.ws_bytes, _stream_ptr(torch))
+        _check(rc, "flrl_rl_decode")
+
+    def result(self):
+        st = int(self.status.item())
+        if st:
+            raise FlrlError(f"flrl_rl_decode: malformed pair stream or output too small (status {st})")
+        return self.out[: int(self.size.item())]
+
+
+def rl_encode_device(d_in, n: int | None = None, prev_run: int = 0):
+    enc = RLEncoder(d_in.numel() if n is None else n)
+    enc.launch(d_in, n, prev_run)
+    return enc.result()
+
+
+def rl_decode_device(d_counts, d_values, out_cap: int):
+    dec = RLDecoder(out_cap, max(d_counts.numel(), 1))
+    dec.launch(d_counts, d_values)
+    return dec.result()
