@@ -220,3 +220,180 @@ def rl_decode_device(d_counts, d_values, out_cap: int):
     dec = RLDecoder(out_cap, max(d_counts.numel(), 1))
     dec.launch(d_counts, d_values)
     return dec.result()
+
+
+# ------------------------------------------------------------------------- host layer
+_szp = C.POINTER(C.c_size_t)
+lib.flrl_host_alloc.restype = _vp
+lib.flrl_host_alloc.argtypes = [_sz]
+lib.flrl_host_free.argtypes = [_vp]
+lib.flrl_free.argtypes = [_vp]
+lib.flrl_last_timing.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
+lib.flrl_set_concat_mode.argtypes = [C.c_int]
+lib.flrl_fl_gpu_compress_into.restype = C.c_int
+lib.flrl_fl_gpu_compress_into.argtypes = [_vp, _sz, C.c_int, _vp, _sz, _vp, _sz, _szp, _szp]
+lib.flrl_fl_gpu_decompress_into.restype = C.c_int
+lib.flrl_fl_gpu_decompress_into.argtypes = [_sz, _vp, _sz, _vp, _sz, C.c_int, _vp, _sz, _szp]
+lib.flrl_rl_gpu_compress_into.restype = C.c_int
+lib.flrl_rl_gpu_compress_into.argtypes = [_vp, _sz, C.c_int, _vp, _vp, _sz, _szp]
+lib.flrl_rl_gpu_decompress_into.restype = C.c_int
+lib.flrl_rl_gpu_decompress_into.argtypes = [_vp, _vp, _sz, C.c_int, _vp, _sz, _szp]
+_u8pp = C.POINTER(_u8p)
+lib.flrl_fl_gpu_compress.restype = C.c_int
+lib.flrl_fl_gpu_compress.argtypes = [_vp, _sz, C.c_int, _u8pp, _szp, _u8pp, _szp]
+lib.flrl_fl_gpu_decompress.restype = C.c_int
+lib.flrl_fl_gpu_decompress.argtypes = [_sz, _vp, _sz, _vp, _sz, C.c_int, _u8pp, _szp]
+lib.flrl_rl_gpu_compress.restype = C.c_int
+lib.flrl_rl_gpu_compress.argtypes = [_vp, _sz, C.c_int, _u8pp, _u8pp, _szp]
+lib.flrl_rl_gpu_decompress.restype = C.c_int
+lib.flrl_rl_gpu_decompress.argtypes = [_vp, _vp, _sz, _sz, C.c_int, _u8pp, _szp]
+for _n in ("fl", "rl"):
+    getattr(lib, f"flrl_{_n}_cpu_compress").restype = C.c_int
+    getattr(lib, f"flrl_{_n}_cpu_decompress").restype = C.c_int
+lib.flrl_fl_cpu_compress.argtypes = [_vp, _sz, _u8pp, _szp, _u8pp, _szp]
+lib.flrl_fl_cpu_decompress.argtypes = [_sz, _vp, _sz, _vp, _sz, _u8pp, _szp]
+lib.flrl_rl_cpu_compress.argtypes = [_vp, _sz, _u8pp, _u8pp, _szp]
+lib.flrl_rl_cpu_decompress.argtypes = [_vp, _vp, _sz, _u8pp, _szp]
+
+
+def _take(ptr, n) -> np.ndarray:
+    """Copy a malloc-owned result out and release it with flrl_free (free(), as the reference's callers do)."""
+    try:
+        return np.ctypeslib.as_array(ptr, (n,)).copy() if n else np.empty(0, np.uint8)
+    finally:
+        lib.flrl_free(ptr)
+
+
+def _np_u8(a) -> np.ndarray:
+    return np.ascontiguousarray(np.frombuffer(a, dtype=np.uint8) if isinstance(a, (bytes, bytearray, memoryview)) else a, dtype=np.uint8)
+
+
+def fl_gpu_compress(data, ngpus: int = 1):
+    """flrl_fl_gpu_compress (the reference's gpuCompress shape): host bytes -> (bits, values) numpy arrays."""
+    a = _np_u8(data)
+    bits, values, nb, nv = _u8p(), _u8p(), C.c_size_t(), C.c_size_t()
+    _check(lib.flrl_fl_gpu_compress(a.ctypes.data, a.size, ngpus, C.byref(bits), C.byref(nb), C.byref(values), C.byref(nv)),
+           "flrl_fl_gpu_compress")
+    return _take(bits, nb.value), _take(values, nv.value)
+
+
+def fl_gpu_decompress(n: int, bits, values, ngpus: int = 1):
+    b, v = _np_u8(bits), _np_u8(values)
+    out, no = _u8p(), C.c_size_t()
+    _check(lib.flrl_fl_gpu_decompress(n, b.ctypes.data, b.size, v.ctypes.data, v.size, ngpus, C.byref(out), C.byref(no)),
+           "flrl_fl_gpu_decompress")
+    return _take(out, no.value)
+
+
+def rl_gpu_compress(data, ngpus: int = 1):
+    a = _np_u8(data)
+    counts, values, p = _u8p(), _u8p(), C.c_size_t()
+    _check(lib.flrl_rl_gpu_compress(a.ctypes.data, a.size, ngpus, C.byref(counts), C.byref(values), C.byref(p)), "flrl_rl_gpu_compress")
+    return _take(counts, p.value), _take(values, p.value)
+
+
+def rl_gpu_decompress(counts, values, expected_size: int = 0, ngpus: int = 1):
+    c, v = _np_u8(counts), _np_u8(values)
+    out, no = _u8p(), C.c_size_t()
+    _check(lib.flrl_rl_gpu_decompress(c.ctypes.data, v.ctypes.data, c.size, expected_size, ngpus, C.byref(out), C.byref(no)),
+           "flrl_rl_gpu_decompress")
+    return _take(out, no.value)
+
+
+def fl_cpu_compress(data):
+    a = _np_u8(data)
+    bits, values, nb, nv = _u8p(), _u8p(), C.c_size_t(), C.c_size_t()
+    _check(lib.flrl_fl_cpu_compress(a.ctypes.data, a.size, C.byref(bits), C.byref(nb), C.byref(values), C.byref(nv)), "flrl_fl_cpu_compress")
+    return _take(bits, nb.value), _take(values, nv.value)
+
+
+def fl_cpu_decompress(n: int, bits, values):
+    b, v = _np_u8(bits), _np_u8(values)
+    out, no = _u8p(), C.c_size_t()
+    _check(lib.flrl_fl_cpu_decompress(n, b.ctypes.data, b.size, v.ctypes.data, v.size, C.byref(out), C.byref(no)), "flrl_fl_cpu_decompress")
+    return _take(out, no.value)
+
+
+def rl_cpu_compress(data):
+    a = _np_u8(data)
+    counts, values, p = _u8p(), _u8p(), C.c_size_t()
+    _check(lib.flrl_rl_cpu_compress(a.ctypes.data, a.size, C.byref(counts), C.byref(values), C.byref(p)), "flrl_rl_cpu_compress")
+    return _take(counts, p.value), _take(values, p.value)
+
+
+def rl_cpu_decompress(counts, values):
+    c, v = _np_u8(counts), _np_u8(values)
+    out, no = _u8p(), C.c_size_t()
+    _check(lib.flrl_rl_cpu_decompress(c.ctypes.data, v.ctypes.data, c.size, C.byref(out), C.byref(no)), "flrl_rl_cpu_decompress")
+    return _take(out, no.value)
+
+
+class PinnedBuffer:
+    """flrl_host_alloc'ed host memory viewed as a numpy array (the host layer copies straight to / from it)."""
+
+    def __init__(self, nbytes: int):
+        self.ptr = lib.flrl_host_alloc(max(nbytes, 1))
+        if not self.ptr:
+            raise FlrlError("flrl_host_alloc failed: " + lib.flrl_last_error().decode(errors="replace"))
+        self.nbytes = nbytes
+        self.array = np.ctypeslib.as_array(C.cast(self.ptr, _u8p), (max(nbytes, 1),))[:nbytes]
+
+    def close(self):
+        if self.ptr:
+            lib.flrl_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        self.close()
+
+
+class HostCodec:
+    """End-to-end round trip through the host layer with pinned HOST buffers (bench.py's e2e leg, the CLI's shape):
+    compress() = flrl_{fl,rl}_gpu_compress_into, decompress() = flrl_{fl,rl}_gpu_decompress_into."""
+
+    def __init__(self, kind: str, n: int, ngpus: int = 1):
+        assert kind in ("fl", "rl")
+        self.kind, self.n, self.ngpus = kind, n, ngpus
+        self.src = PinnedBuffer(n)
+        self.back = PinnedBuffer(n)
+        self.meta = PinnedBuffer((n + 127) // 128 if kind == "fl" else n)  # bits | counts
+        self.payload = PinnedBuffer(n + 16)                                # values
+        self.s0, self.s1 = C.c_size_t(), C.c_size_t()
+        self.out_size = C.c_size_t()
+
+    def load_input(self, src):
+        """src: numpy array or CUDA tensor of n bytes."""
+        if hasattr(src, "cpu"):
+            src = src.cpu().numpy()
+        self.src.array[:] = _np_u8(src)
+
+    def compress(self):
+        if self.kind == "fl":
+            _check(lib.flrl_fl_gpu_compress_into(self.src.ptr, self.n, self.ngpus, self.meta.ptr, self.meta.nbytes, self.payload.ptr,
+                                                 self.payload.nbytes, C.byref(self.s0), C.byref(self.s1)), "flrl_fl_gpu_compress_into")
+        else:
+            _check(lib.flrl_rl_gpu_compress_into(self.src.ptr, self.n, self.ngpus, self.meta.ptr, self.payload.ptr, self.n,
+                                                 C.byref(self.s0)), "flrl_rl_gpu_compress_into")
+            self.s1.value = self.s0.value
+
+    def decompress(self):
+        if self.kind == "fl":
+            _check(lib.flrl_fl_gpu_decompress_into(self.n, self.meta.ptr, self.s0.value, self.payload.ptr, self.s1.value, self.ngpus,
+                                                   self.back.ptr, self.n, C.byref(self.out_size)), "flrl_fl_gpu_decompress_into")
+        else:
+            _check(lib.flrl_rl_gpu_decompress_into(self.meta.ptr, self.payload.ptr, self.s0.value, self.ngpus, self.back.ptr, self.n,
+                                                   C.byref(self.out_size)), "flrl_rl_gpu_decompress_into")
+
+    def compressed(self):
+        return self.meta.array[: self.s0.value], self.payload.array[: self.s1.value]
+
+    def compressed_bytes(self) -> int:
+        return self.s0.value + self.s1.value
+
+    def check_round_trip(self) -> bool:
+        return self.out_size.value == self.n and bool(np.array_equal(self.back.array, self.src.array))
+
+    def timing(self):
+        k, t = C.c_float(), C.c_float()
+        lib.flrl_last_timing(C.byref(k), C.byref(t))
+        return k.value, t.value

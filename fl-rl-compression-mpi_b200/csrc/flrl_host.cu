@@ -1,0 +1,712 @@
+// flrl_host.cu — HOST layer of include/flrl.h: host buffers in, host buffers out.
+//
+// Mirrors the reference's host drivers: FixedLength::gpuCompress / gpuDecompress
+// (/root/reference/src/fl/fl_gpu.cu:289-423, :537-645) and, with ngpus > 1, gpuNCCLCompress
+// (:76-287) — re-designed for one process driving all GPUs of a B200 box:
+//   * device buffers, streams, events and pinned staging are cached per device (the reference
+//     cudaMallocs / cudaFrees every buffer on every call, fl_gpu.cu:320-322, :409-412);
+//   * copies are cudaMemcpyAsync: straight from / to the caller's buffer when it is pinned
+//     (flrl_host_alloc), else through two pinned bounce buffers, double-buffered;
+//   * ngpus > 1: contiguous 128-byte aligned shards (the loadFileMpi rule, file_io.cu:46-51,
+//     in 64-bit arithmetic), one worker thread + one stream per GPU, no data-path collective;
+//     only the per-shard compressed sizes are exchanged — ONE ncclAllGather of a u64 per GPU —
+//     and every GPU then delivers its payload at its exclusive-scan offset (directly to the
+//     host buffer, or peer-copied into GPU 0's buffer first: flrl_set_concat_mode).
+//   * timing is cudaEvent based (the reference's GpuTimer, src/timers/gpu_timer.cu:6-26).
+// No CPU fallback: every failure is reported, never routed to the CPU codec.
+#include <dlfcn.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "abi_common.cuh"
+#include "fl_kernels.cuh"
+#include "rl_kernels.cuh"
+
+using namespace flrl;
+
+namespace {
+
+constexpr size_t BOUNCE = 32u << 20;  // pinned staging chunk for pageable host buffers
+constexpr int MAX_DEV = 16;
+constexpr size_t FRAME_LENGTH_ = FLRL_FRAME_LENGTH;
+
+#define CK(call)                                      \
+    do {                                              \
+        cudaError_t e_ = (call);                      \
+        if (e_ != cudaSuccess) return fail_cuda(e_, #call); \
+    } while (0)
+
+struct DBuf {
+    uint8_t* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n)
+    {
+        n = (n + 255) & ~(size_t)255;
+        if (n <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        CK(cudaMalloc(&p, n));
+        cap = n;
+        return 0;
+    }
+};
+
+struct Dev {
+    int id = -1;
+    bool ready = false;
+    std::mutex mu;
+    cudaStream_t s = nullptr;
+    cudaEvent_t ev[2] = {nullptr, nullptr}, t0 = nullptr, t1 = nullptr, k0 = nullptr, k1 = nullptr;
+    uint8_t* bounce[2] = {nullptr, nullptr};
+    uint64_t* h_scal = nullptr;  // pinned: small results read back from the device
+    DBuf in, a, b, ws, scal, gather;  // device buffers (grow-only)
+    float kernel_ms = 0, total_ms = 0;
+
+    int init(int dev)
+    {
+        if (ready) return 0;
+        id = dev;
+        CK(cudaSetDevice(dev));
+        CK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+        for (auto* e : {&ev[0], &ev[1]}) CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        for (auto* e : {&t0, &t1, &k0, &k1}) CK(cudaEventCreate(e));
+        CK(cudaHostAlloc(&h_scal, 64 * sizeof(uint64_t), cudaHostAllocPortable));
+        if (scal.ensure(64 * sizeof(uint64_t))) return -1;
+        ready = true;
+        return 0;
+    }
+    int need_bounce()
+    {
+        for (int i = 0; i < 2; ++i)
+            if (!bounce[i]) CK(cudaHostAlloc(&bounce[i], BOUNCE, cudaHostAllocPortable));
+        return 0;
+    }
+};
+
+Dev g_dev[MAX_DEV];
+int g_concat_peer = 0;
+std::mutex g_host_mu;  // host-layer calls share the per-device caches: one call at a time
+thread_local float tl_kernel_ms = 0, tl_total_ms = 0;
+
+bool is_pinned(const void* p)
+{
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost;
+}
+
+// host -> device on d.s; pageable sources are staged through the two pinned bounce buffers
+int h2d(Dev& d, void* dst, const void* src, size_t n)
+{
+    if (n == 0) return 0;
+    if (is_pinned(src)) {
+        CK(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, d.s));
+        return 0;
+    }
+    if (d.need_bounce()) return -1;
+    int slot = 0;
+    for (size_t o = 0; o < n; o += BOUNCE, slot ^= 1) {
+        const size_t m = std::min(BOUNCE, n - o);
+        CK(cudaEventSynchronize(d.ev[slot]));  // the copy that last used this buffer has drained
+        memcpy(d.bounce[slot], static_cast<const uint8_t*>(src) + o, m);
+        CK(cudaMemcpyAsync(static_cast<uint8_t*>(dst) + o, d.bounce[slot], m, cudaMemcpyHostToDevice, d.s));
+        CK(cudaEventRecord(d.ev[slot], d.s));
+    }
+    return 0;
+}
+
+// device -> host on d.s; returns after the data is in dst when dst is pageable, else asynchronous
+int d2h(Dev& d, void* dst, const void* src, size_t n)
+{
+    if (n == 0) return 0;
+    if (is_pinned(dst)) {
+        CK(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, d.s));
+        return 0;
+    }
+    if (d.need_bounce()) return -1;
+    size_t prev_o = 0, prev_m = 0;
+    int slot = 0;
+    for (size_t o = 0; o < n; o += BOUNCE, slot ^= 1) {
+        const size_t m = std::min(BOUNCE, n - o);
+        CK(cudaMemcpyAsync(d.bounce[slot], static_cast<const uint8_t*>(src) + o, m, cudaMemcpyDeviceToHost, d.s));
+        CK(cudaEventRecord(d.ev[slot], d.s));
+        if (prev_m) {  // drain the previous chunk while this one is in flight
+            CK(cudaEventSynchronize(d.ev[slot ^ 1]));
+            memcpy(static_cast<uint8_t*>(dst) + prev_o, d.bounce[slot ^ 1], prev_m);
+        }
+        prev_o = o;
+        prev_m = m;
+    }
+    CK(cudaEventSynchronize(d.ev[slot ^ 1]));
+    memcpy(static_cast<uint8_t*>(dst) + prev_o, d.bounce[slot ^ 1], prev_m);
+    return 0;
+}
+
+int device_count(int ngpus, int* out)
+{
+    int have = 0;
+    CK(cudaGetDeviceCount(&have));
+    if (have <= 0) return fail((int)cudaErrorNoDevice, "CUDA Error: no CUDA device (the fl / rl methods have no CPU fallback)");
+    int g = ngpus <= 0 ? have : std::min(ngpus, have);
+    *out = std::min(g, MAX_DEV);
+    return 0;
+}
+
+// contiguous 128-byte aligned shards: per = (n / (128 * G)) * 128, the last shard takes the rest
+// (/root/reference/src/file_io.cu:46-51, in 64-bit arithmetic)
+void shard_range(size_t n, int G, int g, size_t unit, size_t* begin, size_t* len)
+{
+    const size_t per = (n / (unit * (size_t)G)) * unit;
+    *begin = per * (size_t)g;
+    *len = g == G - 1 ? n - *begin : per;
+}
+
+// ---- NCCL, resolved lazily: libflrl.so itself does not depend on libnccl -------------------------
+struct Nccl {
+    void* h = nullptr;
+    void* comms[MAX_DEV + 1][MAX_DEV] = {};  // one communicator set per GPU count
+    bool made[MAX_DEV + 1] = {};
+    int (*CommInitAll)(void**, int, const int*) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    std::mutex mu;
+} g_nccl;
+
+int nccl_ensure(int G)
+{
+    std::lock_guard<std::mutex> lk(g_nccl.mu);
+    if (g_nccl.made[G]) return 0;
+    if (!g_nccl.h) {
+        g_nccl.h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!g_nccl.h) return fail(FLRL_E_ARG, "NCCL Error: cannot load libnccl.so.2: %s", dlerror());
+        g_nccl.CommInitAll = reinterpret_cast<decltype(g_nccl.CommInitAll)>(dlsym(g_nccl.h, "ncclCommInitAll"));
+        g_nccl.AllGather = reinterpret_cast<decltype(g_nccl.AllGather)>(dlsym(g_nccl.h, "ncclAllGather"));
+        g_nccl.GroupStart = reinterpret_cast<decltype(g_nccl.GroupStart)>(dlsym(g_nccl.h, "ncclGroupStart"));
+        g_nccl.GroupEnd = reinterpret_cast<decltype(g_nccl.GroupEnd)>(dlsym(g_nccl.h, "ncclGroupEnd"));
+        g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(dlsym(g_nccl.h, "ncclGetErrorString"));
+        if (!g_nccl.CommInitAll || !g_nccl.AllGather || !g_nccl.GroupStart || !g_nccl.GroupEnd)
+            return fail(FLRL_E_ARG, "NCCL Error: libnccl.so.2 lacks a required symbol");
+    }
+    int devs[MAX_DEV];
+    for (int i = 0; i < G; ++i) devs[i] = i;
+    const int rc = g_nccl.CommInitAll(g_nccl.comms[G], G, devs);
+    if (rc != 0) return fail(FLRL_E_ARG, "NCCL Error: ncclCommInitAll: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
+    g_nccl.made[G] = true;
+    return 0;
+}
+
+// one u64 per GPU (device memory at d.scal + slot) -> all G values in every GPU's d.scal + 8 .. + 8 + G
+int nccl_allgather_sizes(int G)
+{
+    constexpr int ncclUint64_ = 5;  // ncclDataType_t::ncclUint64
+    int rc = g_nccl.GroupStart();
+    for (int g = 0; g < G && rc == 0; ++g) {
+        uint64_t* base = reinterpret_cast<uint64_t*>(g_dev[g].scal.p);
+        rc = g_nccl.AllGather(base, base + 8, 1, ncclUint64_, g_nccl.comms[G][g], g_dev[g].s);
+    }
+    const int rc2 = g_nccl.GroupEnd();
+    if (rc == 0) rc = rc2;
+    if (rc != 0) return fail(FLRL_E_ARG, "NCCL Error: ncclAllGather: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
+    return 0;
+}
+
+}  // namespace
+
+namespace {
+
+// run fn(g) for every shard: inline for one GPU, one worker thread per GPU otherwise
+template <typename F>
+int for_each_gpu(int G, F&& fn)
+{
+    if (G == 1) return fn(0);
+    std::vector<int> rc(G, 0);
+    std::vector<std::string> msg(G);
+    std::vector<std::thread> th;
+    for (int g = 0; g < G; ++g)
+        th.emplace_back([&, g] {
+            rc[g] = fn(g);
+            if (rc[g]) msg[g] = last_error_slot();  // thread-local: carry it back to the caller's thread
+        });
+    for (auto& t : th) t.join();
+    for (int g = 0; g < G; ++g)
+        if (rc[g]) {
+            last_error_slot() = msg[g];
+            return rc[g];
+        }
+    return 0;
+}
+
+void collect_timing(int G)
+{
+    tl_kernel_ms = tl_total_ms = 0;
+    for (int g = 0; g < G; ++g) {
+        tl_kernel_ms = std::max(tl_kernel_ms, g_dev[g].kernel_ms);
+        tl_total_ms = std::max(tl_total_ms, g_dev[g].total_ms);
+    }
+}
+
+int finish_timing(Dev& d)
+{
+    CK(cudaEventRecord(d.t1, d.s));
+    CK(cudaStreamSynchronize(d.s));
+    CK(cudaEventElapsedTime(&d.kernel_ms, d.k0, d.k1));
+    CK(cudaEventElapsedTime(&d.total_ms, d.t0, d.t1));
+    return 0;
+}
+
+// After every GPU has its compressed size in scal[0]: exchange (NCCL all-gather when G > 1), read back.
+// sizes[g] = per-shard size, in the unit the kernel wrote.
+int exchange_sizes(int G, std::vector<uint64_t>& sizes)
+{
+    sizes.assign(G, 0);
+    if (G == 1) {
+        Dev& d = g_dev[0];
+        CK(cudaSetDevice(0));
+        CK(cudaMemcpyAsync(d.h_scal, d.scal.p, sizeof(uint64_t), cudaMemcpyDeviceToHost, d.s));
+        CK(cudaStreamSynchronize(d.s));
+        sizes[0] = d.h_scal[0];
+        return 0;
+    }
+    if (int rc = nccl_ensure(G)) return rc;
+    if (int rc = nccl_allgather_sizes(G)) return rc;
+    for (int g = 0; g < G; ++g) {
+        Dev& d = g_dev[g];
+        CK(cudaSetDevice(g));
+        CK(cudaMemcpyAsync(d.h_scal, d.scal.p + 8 * sizeof(uint64_t), G * sizeof(uint64_t), cudaMemcpyDeviceToHost, d.s));
+    }
+    for (int g = 0; g < G; ++g) {
+        CK(cudaSetDevice(g));
+        CK(cudaStreamSynchronize(g_dev[g].s));
+    }
+    for (int g = 0; g < G; ++g) sizes[g] = g_dev[0].h_scal[g];
+    for (int g = 1; g < G; ++g)  // every rank must have gathered the same vector
+        for (int k = 0; k < G; ++k)
+            if (g_dev[g].h_scal[k] != sizes[k]) return fail(FLRL_E_ARG, "NCCL Error: size all-gather mismatch on GPU %d", g);
+    return 0;
+}
+
+// deliver every shard's payload (device pointer src[g], bytes len[g]) to host dst + off[g]:
+// directly from each GPU, or peer-copied into GPU 0's gather buffer first (one D2H from GPU 0)
+int deliver(int G, uint8_t* dst, const std::vector<const uint8_t*>& src, const std::vector<uint64_t>& off,
+            const std::vector<uint64_t>& len, uint64_t total)
+{
+    if (G > 1 && g_concat_peer) {
+        Dev& d0 = g_dev[0];
+        CK(cudaSetDevice(0));
+        if (d0.gather.ensure(total)) return -1;
+        for (int g = 0; g < G; ++g) {
+            if (!len[g]) continue;
+            CK(cudaSetDevice(g));
+            CK(cudaMemcpyPeerAsync(d0.gather.p + off[g], 0, src[g], g, len[g], g_dev[g].s));
+        }
+        for (int g = 0; g < G; ++g) {
+            CK(cudaSetDevice(g));
+            CK(cudaStreamSynchronize(g_dev[g].s));
+        }
+        CK(cudaSetDevice(0));
+        return d2h(d0, dst, d0.gather.p, total);
+    }
+    return for_each_gpu(G, [&](int g) -> int {
+        CK(cudaSetDevice(g));
+        return d2h(g_dev[g], dst + off[g], src[g], len[g]);
+    });
+}
+
+}  // namespace
+
+extern "C" {
+
+void flrl_set_concat_mode(int peer) { g_concat_peer = peer != 0; }
+
+void* flrl_host_alloc(size_t bytes)
+{
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
+        fail_cuda(cudaGetLastError(), "flrl_host_alloc");
+        return nullptr;
+    }
+    return p;
+}
+void flrl_host_free(void* p)
+{
+    if (p) cudaFreeHost(p);
+}
+void flrl_last_timing(float* kernel_ms, float* total_ms)
+{
+    if (kernel_ms) *kernel_ms = tl_kernel_ms;
+    if (total_ms) *total_ms = tl_total_ms;
+}
+
+// ------------------------------------------------------------------------------------ FL compress
+int flrl_fl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8_t* bits, size_t bits_cap, uint8_t* values,
+                              size_t values_cap, size_t* bits_size, size_t* values_size)
+{
+    if (!bits_size || !values_size) return fail(FLRL_E_ARG, "flrl_fl_gpu_compress: NULL size output");
+    *bits_size = *values_size = 0;
+    if (size == 0) return FLRL_OK;  // fl_gpu.cu:291-294
+    if (!data) return fail(FLRL_E_ARG, "flrl_fl_gpu_compress: NULL input");
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    int G = 1;
+    if (int rc = device_count(ngpus, &G)) return rc;
+    if (size < (size_t)G * 16384) G = 1;
+    const size_t frames = (size + FRAME_LENGTH_ - 1) / FRAME_LENGTH_;
+    if (bits_cap < frames) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_compress: bits capacity %zu < %zu", bits_cap, frames);
+
+    int rc = for_each_gpu(G, [&](int g) -> int {
+        Dev& d = g_dev[g];
+        CK(cudaSetDevice(g));
+        if (d.init(g)) return -1;
+        size_t b0, n;
+        shard_range(size, G, g, 128, &b0, &n);
+        const size_t n16 = (n + 15) & ~(size_t)15;
+        if (d.in.ensure(n16) || d.a.ensure((n + 127) / 128) || d.b.ensure(n16) || d.ws.ensure(fl_workspace_bytes(n))) return -1;
+        CK(cudaEventRecord(d.t0, d.s));
+        if (h2d(d, d.in.p, data + b0, n)) return -1;
+        CK(cudaEventRecord(d.k0, d.s));
+        CK(fl_encode_launch(d.in.p, n, d.a.p, d.b.p, reinterpret_cast<uint64_t*>(d.scal.p), d.ws.p, d.s));
+        CK(cudaEventRecord(d.k1, d.s));
+        return 0;
+    });
+    if (rc) return rc;
+    std::vector<uint64_t> sizes;
+    if ((rc = exchange_sizes(G, sizes))) return rc;
+    std::vector<uint64_t> voff(G), boff(G), blen(G);
+    std::vector<const uint8_t*> vsrc(G), bsrc(G);
+    uint64_t total = 0;
+    for (int g = 0; g < G; ++g) {
+        size_t b0, n;
+        shard_range(size, G, g, 128, &b0, &n);
+        voff[g] = total;  // exclusive scan of the gathered sizes
+        total += sizes[g];
+        boff[g] = b0 / 128;
+        blen[g] = (n + 127) / 128;
+        vsrc[g] = g_dev[g].b.p;
+        bsrc[g] = g_dev[g].a.p;
+    }
+    if (values_cap < total) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_compress: values capacity %zu < %llu", values_cap, (unsigned long long)total);
+    if ((rc = deliver(G, bits, bsrc, boff, blen, frames))) return rc;
+    if ((rc = deliver(G, values, vsrc, voff, sizes, total))) return rc;
+    for (int g = 0; g < G; ++g) {
+        CK(cudaSetDevice(g));
+        if (finish_timing(g_dev[g])) return -1;
+    }
+    collect_timing(G);
+    *bits_size = frames;
+    *values_size = total;
+    return FLRL_OK;
+}
+
+int flrl_fl_gpu_compress(const uint8_t* data, size_t size, int ngpus, uint8_t** bits, size_t* bits_size, uint8_t** values,
+                         size_t* values_size)
+{
+    if (!bits || !values) return fail(FLRL_E_ARG, "flrl_fl_gpu_compress: NULL output");
+    *bits = *values = nullptr;
+    if (size == 0) {
+        if (bits_size) *bits_size = 0;
+        if (values_size) *values_size = 0;
+        return FLRL_OK;
+    }
+    const size_t frames = (size + FRAME_LENGTH_ - 1) / FRAME_LENGTH_;
+    uint8_t* b = static_cast<uint8_t*>(malloc(frames));
+    uint8_t* v = static_cast<uint8_t*>(malloc(size + 16));  // worst case: every frame 8 bits wide
+    if (!b || !v) {
+        free(b);
+        free(v);
+        return fail(FLRL_E_NOMEM, "flrl_fl_gpu_compress: out of memory");
+    }
+    const int rc = flrl_fl_gpu_compress_into(data, size, ngpus, b, frames, v, size + 16, bits_size, values_size);
+    if (rc) {
+        free(b);
+        free(v);
+        return rc;
+    }
+    uint8_t* shrunk = static_cast<uint8_t*>(realloc(v, *values_size ? *values_size : 1));
+    *bits = b;
+    *values = shrunk ? shrunk : v;
+    return FLRL_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// ---------------------------------------------------------------------------------- FL decompress
+int flrl_fl_gpu_decompress_into(size_t output_size, const uint8_t* bits, size_t bits_size, const uint8_t* values,
+                                size_t values_size, int ngpus, uint8_t* out, size_t out_cap, size_t* out_size)
+{
+    if (!out_size) return fail(FLRL_E_ARG, "flrl_fl_gpu_decompress: NULL size output");
+    *out_size = 0;
+    if (output_size == 0 || bits_size == 0 || values_size == 0) return FLRL_OK;  // fl_gpu.cu:539-543
+    if (!bits || !values || !out) return fail(FLRL_E_ARG, "flrl_fl_gpu_decompress: NULL buffer");
+    const size_t frames = (output_size + FRAME_LENGTH_ - 1) / FRAME_LENGTH_;
+    if (bits_size != frames) return fail(FLRL_E_FORMAT, "flrl_fl_gpu_decompress: bitsSize != ceil(outputSize/128)");
+    if (out_cap < output_size) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_decompress: output capacity too small");
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    int G = 1;
+    if (int rc = device_count(ngpus, &G)) return rc;
+    if (output_size < (size_t)G * 16384) G = 1;
+
+    // phase A: widths of each shard to its GPU, sum of widths -> value bytes of the shard
+    int rc = for_each_gpu(G, [&](int g) -> int {
+        Dev& d = g_dev[g];
+        CK(cudaSetDevice(g));
+        if (d.init(g)) return -1;
+        size_t b0, n;
+        shard_range(output_size, G, g, 128, &b0, &n);
+        const size_t nf = (n + 127) / 128;
+        if (d.a.ensure(nf + 16)) return -1;
+        CK(cudaEventRecord(d.t0, d.s));
+        if (h2d(d, d.a.p, bits + b0 / 128, nf)) return -1;
+        CK(sum_bytes_launch(d.a.p, n / 128, reinterpret_cast<uint64_t*>(d.scal.p), d.s));  // full frames only
+        return 0;
+    });
+    if (rc) return rc;
+    std::vector<uint64_t> sums;
+    if ((rc = exchange_sizes(G, sums))) return rc;
+    std::vector<uint64_t> voff(G), vlen(G);
+    uint64_t total = 0;
+    for (int g = 0; g < G; ++g) {
+        voff[g] = total;
+        vlen[g] = 16 * sums[g];
+        if (g == G - 1 && output_size % 128) vlen[g] += ((output_size % 128) * bits[frames - 1] + 7) / 8;
+        total += vlen[g];
+    }
+    if (total > values_size) return fail(FLRL_E_FORMAT, "flrl_fl_gpu_decompress: values shorter than the widths imply");
+    // phase B: values of each shard to its GPU, decode, output back
+    rc = for_each_gpu(G, [&](int g) -> int {
+        Dev& d = g_dev[g];
+        CK(cudaSetDevice(g));
+        size_t b0, n;
+        shard_range(output_size, G, g, 128, &b0, &n);
+        const size_t nf = (n + 127) / 128;
+        if (d.in.ensure(vlen[g] + 16) || d.b.ensure(n + 16) || d.ws.ensure(fl_workspace_bytes(n))) return -1;
+        if (h2d(d, d.in.p, values + voff[g], vlen[g])) return -1;
+        CK(cudaEventRecord(d.k0, d.s));
+        CK(fl_decode_launch(d.a.p, nf, d.in.p, vlen[g], d.b.p, n, d.ws.p, d.s));
+        CK(cudaEventRecord(d.k1, d.s));
+        CK(cudaMemcpyAsync(d.h_scal + 32, fl_decode_status(d.ws.p, n), sizeof(int), cudaMemcpyDeviceToHost, d.s));
+        if (d2h(d, out + b0, d.b.p, n)) return -1;
+        if (finish_timing(d)) return -1;
+        if (*reinterpret_cast<int*>(d.h_scal + 32)) return fail(FLRL_E_FORMAT, "flrl_fl_gpu_decompress: malformed container (GPU %d)", g);
+        return 0;
+    });
+    if (rc) return rc;
+    collect_timing(G);
+    *out_size = output_size;
+    return FLRL_OK;
+}
+
+int flrl_fl_gpu_decompress(size_t output_size, const uint8_t* bits, size_t bits_size, const uint8_t* values,
+                           size_t values_size, int ngpus, uint8_t** out, size_t* out_size)
+{
+    if (!out || !out_size) return fail(FLRL_E_ARG, "flrl_fl_gpu_decompress: NULL output");
+    *out = nullptr;
+    *out_size = 0;
+    if (output_size == 0 || bits_size == 0 || values_size == 0) return FLRL_OK;
+    uint8_t* o = static_cast<uint8_t*>(malloc(output_size));
+    if (!o) return fail(FLRL_E_NOMEM, "flrl_fl_gpu_decompress: out of memory");
+    const int rc = flrl_fl_gpu_decompress_into(output_size, bits, bits_size, values, values_size, ngpus, o, output_size, out_size);
+    if (rc) {
+        free(o);
+        return rc;
+    }
+    *out = o;
+    return FLRL_OK;
+}
+
+// ------------------------------------------------------------------------------------ RL compress
+int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8_t* counts, uint8_t* values, size_t pair_cap,
+                              size_t* pairs)
+{
+    if (!pairs) return fail(FLRL_E_ARG, "flrl_rl_gpu_compress: NULL size output");
+    *pairs = 0;
+    if (size == 0) return FLRL_OK;
+    if (!data || !counts || !values) return fail(FLRL_E_ARG, "flrl_rl_gpu_compress: NULL buffer");
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    int G = 1;
+    if (int rc = device_count(ngpus, &G)) return rc;
+    if (size < (size_t)G * 16384) G = 1;
+    int rc = for_each_gpu(G, [&](int g) -> int {
+        Dev& d = g_dev[g];
+        CK(cudaSetDevice(g));
+        if (d.init(g)) return -1;
+        size_t b0, n;
+        shard_range(size, G, g, 128, &b0, &n);
+        // bytes equal to the shard's first byte immediately before it: the run the shard continues
+        uint64_t prev = 0;
+        while (prev < b0 && data[b0 - 1 - prev] == data[b0]) ++prev;
+        const size_t ahead = std::min<size_t>(255, size - (b0 + n));  // look-ahead: a pair that starts here gets its full count
+        const size_t n16 = (n + 15) & ~(size_t)15;
+        if (d.in.ensure(n + ahead + 16) || d.a.ensure(n16) || d.b.ensure(n16) || d.ws.ensure(rl_encode_workspace_bytes(n))) return -1;
+        CK(cudaEventRecord(d.t0, d.s));
+        if (h2d(d, d.in.p, data + b0, n + ahead)) return -1;
+        CK(cudaEventRecord(d.k0, d.s));
+        CK(rl_encode_launch(d.in.p, n, n + ahead, prev, d.a.p, d.b.p, n16, reinterpret_cast<uint64_t*>(d.scal.p), d.ws.p, d.s));
+        CK(cudaEventRecord(d.k1, d.s));
+        return 0;
+    });
+    if (rc) return rc;
+    std::vector<uint64_t> sizes;
+    if ((rc = exchange_sizes(G, sizes))) return rc;
+    std::vector<uint64_t> off(G);
+    std::vector<const uint8_t*> csrc(G), vsrc(G);
+    uint64_t total = 0;
+    for (int g = 0; g < G; ++g) {
+        off[g] = total;
+        total += sizes[g];
+        csrc[g] = g_dev[g].a.p;
+        vsrc[g] = g_dev[g].b.p;
+    }
+    if (pair_cap < total) return fail(FLRL_E_CAPACITY, "flrl_rl_gpu_compress: pair capacity %zu < %llu", pair_cap, (unsigned long long)total);
+    if ((rc = deliver(G, counts, csrc, off, sizes, total))) return rc;
+    if ((rc = deliver(G, values, vsrc, off, sizes, total))) return rc;
+    for (int g = 0; g < G; ++g) {
+        CK(cudaSetDevice(g));
+        if (finish_timing(g_dev[g])) return -1;
+    }
+    collect_timing(G);
+    *pairs = total;
+    return FLRL_OK;
+}
+
+int flrl_rl_gpu_compress(const uint8_t* data, size_t size, int ngpus, uint8_t** counts, uint8_t** values, size_t* pairs)
+{
+    if (!counts || !values || !pairs) return fail(FLRL_E_ARG, "flrl_rl_gpu_compress: NULL output");
+    *counts = *values = nullptr;
+    *pairs = 0;
+    if (size == 0) return FLRL_OK;
+    uint8_t* c = static_cast<uint8_t*>(malloc(size));
+    uint8_t* v = static_cast<uint8_t*>(malloc(size));
+    if (!c || !v) {
+        free(c);
+        free(v);
+        return fail(FLRL_E_NOMEM, "flrl_rl_gpu_compress: out of memory");
+    }
+    const int rc = flrl_rl_gpu_compress_into(data, size, ngpus, c, v, size, pairs);
+    if (rc) {
+        free(c);
+        free(v);
+        return rc;
+    }
+    uint8_t* c2 = static_cast<uint8_t*>(realloc(c, *pairs ? *pairs : 1));
+    uint8_t* v2 = static_cast<uint8_t*>(realloc(v, *pairs ? *pairs : 1));
+    *counts = c2 ? c2 : c;
+    *values = v2 ? v2 : v;
+    return FLRL_OK;
+}
+
+// ---------------------------------------------------------------------------------- RL decompress
+int flrl_rl_gpu_decompress_into(const uint8_t* counts, const uint8_t* values, size_t pairs, int ngpus, uint8_t* out,
+                                size_t out_cap, size_t* out_size)
+{
+    if (!out_size) return fail(FLRL_E_ARG, "flrl_rl_gpu_decompress: NULL size output");
+    *out_size = 0;
+    if (pairs == 0) return FLRL_OK;
+    if (!counts || !values || !out) return fail(FLRL_E_ARG, "flrl_rl_gpu_decompress: NULL buffer");
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    int G = 1;
+    if (int rc = device_count(ngpus, &G)) return rc;
+    if (pairs < (size_t)G * 4096) G = 1;
+    // phase A: pairs of each shard to its GPU, sum of counts -> output bytes of the shard
+    int rc = for_each_gpu(G, [&](int g) -> int {
+        Dev& d = g_dev[g];
+        CK(cudaSetDevice(g));
+        if (d.init(g)) return -1;
+        size_t p0, np;
+        shard_range(pairs, G, g, 16, &p0, &np);
+        if (d.a.ensure(np + 16) || d.b.ensure(np + 16) || d.ws.ensure(rl_decode_workspace_bytes(np))) return -1;
+        CK(cudaEventRecord(d.t0, d.s));
+        if (h2d(d, d.a.p, counts + p0, np) || h2d(d, d.b.p, values + p0, np)) return -1;
+        CK(sum_bytes_launch(d.a.p, np, reinterpret_cast<uint64_t*>(d.scal.p), d.s));
+        return 0;
+    });
+    if (rc) return rc;
+    std::vector<uint64_t> olen;
+    if ((rc = exchange_sizes(G, olen))) return rc;
+    std::vector<uint64_t> ooff(G);
+    uint64_t total = 0;
+    for (int g = 0; g < G; ++g) {
+        ooff[g] = total;
+        total += olen[g];
+    }
+    if (total > out_cap) return fail(FLRL_E_CAPACITY, "flrl_rl_gpu_decompress: decoded size %llu exceeds the output capacity %zu",
+                                     (unsigned long long)total, out_cap);
+    rc = for_each_gpu(G, [&](int g) -> int {
+        Dev& d = g_dev[g];
+        CK(cudaSetDevice(g));
+        size_t p0, np;
+        shard_range(pairs, G, g, 16, &p0, &np);
+        if (d.in.ensure(olen[g] + 16)) return -1;
+        uint64_t* d_size = reinterpret_cast<uint64_t*>(d.scal.p) + 40;
+        CK(cudaEventRecord(d.k0, d.s));
+        CK(rl_decode_launch(d.a.p, d.b.p, np, d.in.p, olen[g], d_size, d.ws.p, d.s));
+        CK(cudaEventRecord(d.k1, d.s));
+        CK(cudaMemcpyAsync(d.h_scal + 32, rl_decode_status(d.ws.p, np), sizeof(int), cudaMemcpyDeviceToHost, d.s));
+        if (d2h(d, out + ooff[g], d.in.p, olen[g])) return -1;
+        if (finish_timing(d)) return -1;
+        if (*reinterpret_cast<int*>(d.h_scal + 32)) return fail(FLRL_E_FORMAT, "flrl_rl_gpu_decompress: malformed pair stream (GPU %d)", g);
+        return 0;
+    });
+    if (rc) return rc;
+    collect_timing(G);
+    *out_size = total;
+    return FLRL_OK;
+}
+
+int flrl_rl_gpu_decompress(const uint8_t* counts, const uint8_t* values, size_t pairs, size_t expected_size, int ngpus,
+                           uint8_t** out, size_t* out_size)
+{
+    if (!out || !out_size) return fail(FLRL_E_ARG, "flrl_rl_gpu_decompress: NULL output");
+    *out = nullptr;
+    *out_size = 0;
+    if (pairs == 0) return FLRL_OK;
+    const size_t cap = expected_size ? expected_size : pairs * 255;
+    uint8_t* o = static_cast<uint8_t*>(malloc(cap));
+    if (!o) return fail(FLRL_E_NOMEM, "flrl_rl_gpu_decompress: out of memory");
+    const int rc = flrl_rl_gpu_decompress_into(counts, values, pairs, ngpus, o, cap, out_size);
+    if (rc) {
+        free(o);
+        return rc;
+    }
+    *out = o;
+    return FLRL_OK;
+}
+
+// release every cached device buffer, stream and pinned staging buffer
+void flrl_release(void)
+{
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    for (int g = 0; g < MAX_DEV; ++g) {
+        Dev& d = g_dev[g];
+        if (!d.ready) continue;
+        cudaSetDevice(g);
+        cudaStreamSynchronize(d.s);
+        for (DBuf* b : {&d.in, &d.a, &d.b, &d.ws, &d.scal, &d.gather}) {
+            if (b->p) cudaFree(b->p);
+            b->p = nullptr;
+            b->cap = 0;
+        }
+        for (auto& p : d.bounce) {
+            if (p) cudaFreeHost(p);
+            p = nullptr;
+        }
+        if (d.h_scal) cudaFreeHost(d.h_scal);
+        d.h_scal = nullptr;
+        for (cudaEvent_t e : {d.ev[0], d.ev[1], d.t0, d.t1, d.k0, d.k1}) cudaEventDestroy(e);
+        cudaStreamDestroy(d.s);
+        d.ready = false;
+    }
+}
+
+}  // extern "C"

@@ -20,6 +20,8 @@
 // 255 bytes, so tiles and shards concatenate to the single-stream output byte for byte.
 #include "rl_kernels.cuh"
 
+#include <algorithm>
+
 #include "flrl_bits.cuh"
 #include "lookback.cuh"
 
@@ -465,6 +467,31 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
             }
         }
     }
+}
+
+// ---- sum of a byte array (shard offsets of the decoders: sum of widths / sum of counts) ------
+__global__ void __launch_bounds__(256) sum_bytes_kernel(const uint8_t* __restrict__ p, size_t n, unsigned long long* __restrict__ out)
+{
+    unsigned long long acc = 0;
+    const size_t n16 = n / 16;
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = q[i];
+        acc += byte_sum4(v.x) + byte_sum4(v.y) + byte_sum4(v.z) + byte_sum4(v.w);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 15)) acc += p[n16 * 16 + threadIdx.x];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
+cudaError_t sum_bytes_launch(const uint8_t* d_p, size_t n, uint64_t* d_sum, cudaStream_t stream)
+{
+    cudaError_t e = cudaMemsetAsync(d_sum, 0, sizeof(uint64_t), stream);
+    if (e != cudaSuccess || n == 0) return e;
+    const unsigned blocks = (unsigned)std::min<size_t>((n / 16 + 255) / 256 + 1, 148 * 8);
+    sum_bytes_kernel<<<blocks, 256, 0, stream>>>(d_p, n, reinterpret_cast<unsigned long long*>(d_sum));
+    return cudaGetLastError();
 }
 
 // =============================================================================================

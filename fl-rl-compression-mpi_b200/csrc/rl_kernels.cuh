@@ -17,5 +17,7 @@ cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint
 cudaError_t rl_decode_launch(const uint8_t* d_counts, const uint8_t* d_values, size_t pairs, uint8_t* d_out, size_t out_cap,
                              uint64_t* d_out_size, void* d_ws, cudaStream_t stream);
 const int* rl_decode_status(const void* d_ws, size_t pairs);
+// *d_sum = sum of the n bytes at d_p (16-byte aligned)
+cudaError_t sum_bytes_launch(const uint8_t* d_p, size_t n, uint64_t* d_sum, cudaStream_t stream);
 
 }  // namespace flrl

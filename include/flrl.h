@@ -136,6 +136,29 @@ int flrl_rl_gpu_compress(const uint8_t* data, size_t size, int ngpus, uint8_t** 
 int flrl_rl_gpu_decompress(const uint8_t* counts, const uint8_t* values, size_t pairs, size_t expected_size, int ngpus,
                            uint8_t** out, size_t* out_size);
 
+/*
+ * Caller-provided outputs (extension; no reference counterpart): same behaviour, but results are written into
+ * buffers the caller owns.  When those — and the inputs — come from flrl_host_alloc (pinned), every
+ * cudaMemcpyAsync goes straight to / from them and the bounce copy is skipped; this is what the CLI's file
+ * staging and bench.py's end-to-end leg use.  FLRL_E_CAPACITY if an output does not fit.
+ */
+int flrl_fl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8_t* bits, size_t bits_cap, uint8_t* values,
+                              size_t values_cap, size_t* bits_size, size_t* values_size);
+int flrl_fl_gpu_decompress_into(size_t output_size, const uint8_t* bits, size_t bits_size, const uint8_t* values,
+                                size_t values_size, int ngpus, uint8_t* out, size_t out_cap, size_t* out_size);
+int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8_t* counts, uint8_t* values, size_t pair_cap,
+                              size_t* pairs);
+int flrl_rl_gpu_decompress_into(const uint8_t* counts, const uint8_t* values, size_t pairs, int ngpus, uint8_t* out,
+                                size_t out_cap, size_t* out_size);
+
+/* ngpus > 1: how shard payloads are concatenated after the NCCL all-gather of their sizes.
+ * 0 (default): every GPU copies its payload straight to its offset in the host buffer (8 PCIe links in parallel);
+ * 1: every GPU peer-copies (cudaMemcpyPeerAsync over NVLink) into GPU 0's buffer, which is then copied to the
+ *    host once — the device-resident merge of gpuNCCLCompress (fl_gpu.cu:221-238, :280). */
+void flrl_set_concat_mode(int peer);
+/* Frees the per-device caches (buffers, streams, pinned staging) the host layer keeps between calls. */
+void flrl_release(void);
+
 /* CPU methods of the CLI (`fl-cpu`, `rl-cpu`): FixedLength::cpuCompress / cpuDecompress
  * (fl_cpu.cu:9-147) and the RL spec.  These ARE CPU methods by definition; the GPU entry
  * points above never route through them. */
