@@ -1,0 +1,315 @@
+// fl_decode.cu — fixed-length decoder for sm_100a: persistent CTAs, contiguous ranges, TMA pipeline.
+//
+// Replaces compressInitializeFrameStartIndiciesBits + thrust::exclusive_scan + decompressCalculateOutput
+// (/root/reference/src/fl/fl_gpu.cu:687-698, :805-808, :728-755) with one launch.
+//
+// Where a frame's values start depends only on the widths array (N/128 bytes), not on the payload,
+// so no per-tile look-back is needed:
+//   * grid = 2 CTAs per SM (all co-resident); CTA c owns a CONTIGUOUS range of 128-frame tiles;
+//   * phase 0: the CTA sums the widths of its range (a few tens of KiB, coalesced 16-byte loads),
+//     publishes the sum and reads its predecessors' sums once (one look-back per CTA, not per tile);
+//   * phase 1: a producer warp walks the range with a running offset: one 512-byte coalesced load
+//     brings the widths of 4 tiles, a segmented warp scan gives every frame's offset, and for each
+//     tile one TMA bulk copy of exactly its 16*sum(b) value bytes is issued into a ring of
+//     FLD_STAGES shared-memory stages (full / free mbarriers) — several tiles are always in flight;
+//   * 8 unpack warps wait on the stage's mbarrier, pull their words into registers, release the
+//     stage, unpack lane-locally (flrl_bits.cuh) and store 2 x 16 bytes per lane: a warp writes
+//     1 KiB of contiguous output per item, no staging buffer, no store-side synchronisation.
+#include <stdlib.h>
+
+#include <algorithm>
+
+#include "fl_kernels.cuh"
+#include "flrl_bits.cuh"
+#include "lookback.cuh"
+
+namespace flrl {
+
+static constexpr int FLD_TILE_FRAMES = 128;
+static constexpr int FLD_TILE_BYTES = FLD_TILE_FRAMES * 128;  // 16 KiB of output per tile
+static constexpr int FLD_STAGES = 5;
+static constexpr int FLD_UNPACK_THREADS = 256;
+static constexpr int FLD_THREADS = FLD_UNPACK_THREADS + 32;   // + producer warp
+static constexpr int FLD_ITEMS = FLD_TILE_BYTES / 32 / FLD_UNPACK_THREADS;  // 32-byte items per thread per tile = 2
+static constexpr int FLD_STAGE_BYTES = FLD_TILE_BYTES + 128;  // slack for the unpacker's over-reads
+static constexpr int FLD_CTAS_PER_SM = 2;
+
+struct __align__(16) FldMeta {
+    uint16_t off[FLD_TILE_FRAMES];  // exclusive prefix of widths inside the tile (16-byte units)
+    uint8_t b[FLD_TILE_FRAMES];     // width, 0 = no frame here
+};
+
+// widths of frames [f, f + 16) as 16 bytes; frames at or past `fend` read as 0
+__device__ __forceinline__ uint4 ld_widths16(const uint8_t* __restrict__ bits, size_t f, size_t fend, bool aligned)
+{
+    if (aligned && f + 16 <= fend) return *reinterpret_cast<const uint4*>(bits + f);
+    uint32_t w[4] = {0, 0, 0, 0};
+    for (int i = 0; i < 16; ++i)
+        if (f + i < fend) w[i >> 2] |= (uint32_t)bits[f + i] << (8 * (i & 3));
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+// clamp every width byte to 8 and report whether any of the `valid` leading bytes was 0 or > 8
+__device__ __forceinline__ uint4 clamp_widths(uint4 q, int valid, bool& bad)
+{
+    uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int v = valid - 4 * k;
+        const uint32_t keep = v >= 4 ? ~0u : (v <= 0 ? 0u : ((1u << (8 * v)) - 1u));
+        const uint32_t c = __vminu4(w[k], 0x08080808u);
+        const uint32_t nz = (((c & 0x7f7f7f7fu) + 0x7f7f7f7fu) | c) & 0x80808080u;  // high bit: byte non-zero
+        bad = bad || (((c ^ w[k]) | (~nz & 0x80808080u)) & keep) != 0;
+        w[k] = c & keep;
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __forceinline__ uint32_t sum_bytes16(uint4 q)
+{
+    const uint32_t a = (q.x & 0x00ff00ffu) + ((q.x >> 8) & 0x00ff00ffu) + (q.y & 0x00ff00ffu) + ((q.y >> 8) & 0x00ff00ffu) +
+                       (q.z & 0x00ff00ffu) + ((q.z >> 8) & 0x00ff00ffu) + (q.w & 0x00ff00ffu) + ((q.w >> 8) & 0x00ff00ffu);
+    return (a & 0xffffu) + (a >> 16);
+}
+
+// one look-back per CTA over 64-bit sums (called by one full warp)
+__device__ __forceinline__ uint64_t lookback_sum64(const uint64_t* desc, int idx, int lane)
+{
+    uint64_t excl = 0;
+    int j = idx - 1 - lane;
+    while (true) {
+        uint64_t v;
+        do {
+            v = j >= 0 ? ld_relaxed_u64(desc + j) : LB_INC;
+        } while (__any_sync(0xffffffffu, (v >> 62) == 0));
+        const unsigned incm = __ballot_sync(0xffffffffu, (v >> 62) == 2);
+        if (incm) {
+            const int first = __ffs(incm) - 1;
+            return excl + warp_sum_u64(lane <= first ? (v & LB_MASK) : 0ull);
+        }
+        excl += warp_sum_u64(v & LB_MASK);
+        j -= 32;
+    }
+}
+
+// fl_cpu.cu:117-141 for the final partial frame (len = n % 128), FLD_THREADS threads
+__device__ __noinline__ void decode_tail_frame(const uint8_t* vin, uint32_t avail, uint32_t len, uint32_t b, uint8_t* out)
+{
+    const int tid = threadIdx.x;
+    if (tid < (int)len && b >= 1 && b <= 8) {
+        const uint32_t bit = tid * b;
+        const uint32_t byte = bit >> 3, sh = bit & 7;
+        uint32_t v = byte < avail ? vin[byte] : 0u;
+        if (byte + 1 < avail) v |= (uint32_t)vin[byte + 1] << 8;
+        out[tid] = (uint8_t)((v >> sh) & ((1u << b) - 1u));
+    }
+}
+
+__device__ __forceinline__ size_t umin64(size_t a, size_t b) { return a < b ? a : b; }
+
+__global__ void __launch_bounds__(FLD_THREADS, FLD_CTAS_PER_SM)
+fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t* __restrict__ values, size_t nvalues,
+                 uint8_t* __restrict__ out, size_t n, uint64_t* __restrict__ desc, int* __restrict__ err, long long tiles)
+{
+    extern __shared__ __align__(128) uint8_t smem[];  // FLD_STAGES x FLD_STAGE_BYTES
+    __shared__ FldMeta meta[FLD_STAGES];
+    __shared__ __align__(8) uint64_t full[FLD_STAGES], freeb[FLD_STAGES];
+    __shared__ uint32_t wsum[FLD_THREADS / 32];
+    __shared__ uint64_t range_end;  // value offset (16-byte units) after the CTA's last full frame
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long G = gridDim.x, c = blockIdx.x;
+    const long long t0 = tiles * c / G, t1 = tiles * (c + 1) / G, T = t1 - t0;
+    const size_t full_frames = n / FRAME;
+    const size_t fbeg = (size_t)t0 * FLD_TILE_FRAMES;
+    const size_t fend = umin64((size_t)t1 * FLD_TILE_FRAMES, full_frames);
+    const bool aligned = (reinterpret_cast<uintptr_t>(bits) & 15) == 0;
+
+    if (tid == 0) {
+        for (int s = 0; s < FLD_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&freeb[s], FLD_UNPACK_THREADS / 32);
+        }
+        fence_mbar_init();
+    }
+    // ---- phase 0: sum of the widths of the range ------------------------------------------------
+    {
+        uint32_t acc = 0;
+        bool bad = false;
+        for (size_t f = fbeg + (size_t)tid * 16; f < fend; f += (size_t)FLD_THREADS * 16) {
+            const uint4 q = clamp_widths(ld_widths16(bits, f, fend, aligned), (int)umin64(16, fend - f), bad);
+            acc += sum_bytes16(q);
+        }
+        if (bad) atomicExch(err, 1);  // a width outside 1..8: malformed container
+        acc = __reduce_add_sync(0xffffffffu, acc);
+        if (lane == 0) wsum[warp] = acc;
+    }
+    __syncthreads();
+
+    if (warp == FLD_UNPACK_THREADS / 32) {
+        // =============================== producer warp =====================================
+        uint64_t total = 0;
+#pragma unroll
+        for (int k = 0; k < FLD_THREADS / 32; ++k) total += wsum[k];
+        uint64_t base = 0;
+        if (c > 0) {
+            if (lane == 0) st_relaxed_u64(desc + c, LB_AGG | total);
+            base = lookback_sum64(desc, (int)c, lane);
+        }
+        if (lane == 0) {
+            st_relaxed_u64(desc + c, LB_INC | (base + total));
+            range_end = base + total;
+        }
+        const uint64_t nv16 = nvalues / 16;
+        const int sub = lane >> 3, part = lane & 7;
+        auto load_batch = [&](long long kb) -> uint4 {
+            const long long k = 4 * kb + sub;
+            return k < T ? ld_widths16(bits, (size_t)(t0 + k) * FLD_TILE_FRAMES + part * 16, fend, aligned) : make_uint4(0, 0, 0, 0);
+        };
+        uint4 qn = load_batch(0);
+        for (long long kb = 0; 4 * kb < T; ++kb) {
+            uint4 q = qn;
+            qn = load_batch(kb + 1);  // widths of the next 4 tiles are in flight while these are issued
+            const size_t f = (size_t)(t0 + 4 * kb + sub) * FLD_TILE_FRAMES + part * 16;
+            bool bad = false;
+            q = clamp_widths(q, f < fend ? (int)umin64(16, fend - f) : 0, bad);
+            const uint32_t s16 = sum_bytes16(q);
+            uint32_t inc = s16;
+#pragma unroll
+            for (int d = 1; d < 8; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (part >= d) inc += o;
+            }
+            uint32_t run = inc - s16;  // exclusive offset of this lane's 16 frames inside its tile
+            const uint32_t w4[4] = {q.x, q.y, q.z, q.w};
+            uint32_t o16[8];
+#pragma unroll
+            for (int i = 0; i < 16; i += 2) {
+                const uint32_t b0 = (w4[i >> 2] >> (8 * (i & 3))) & 0xffu, b1 = (w4[i >> 2] >> (8 * (i & 3) + 8)) & 0xffu;
+                o16[i >> 1] = run | ((run + b0) << 16);
+                run += b0 + b1;
+            }
+#pragma unroll
+            for (int s2 = 0; s2 < 4; ++s2) {
+                const long long k = 4 * kb + s2;
+                if (k >= T) break;
+                const int s = (int)(k % FLD_STAGES);
+                const long long it = k / FLD_STAGES;
+                if (it > 0) mbar_wait(&freeb[s], (uint32_t)(it - 1) & 1u);  // the unpack warps have drained tile k - STAGES
+                if (sub == s2) {
+                    reinterpret_cast<uint4*>(meta[s].b)[part] = q;
+                    reinterpret_cast<uint4*>(meta[s].off)[2 * part] = make_uint4(o16[0], o16[1], o16[2], o16[3]);
+                    reinterpret_cast<uint4*>(meta[s].off)[2 * part + 1] = make_uint4(o16[4], o16[5], o16[6], o16[7]);
+                }
+                const uint32_t tot = __shfl_sync(0xffffffffu, inc, 8 * s2 + 7);
+                __syncwarp();
+                if (lane == 0) {
+                    uint64_t units = tot;
+                    if (base + units > nv16) {  // values shorter than the widths imply: never read past the array
+                        atomicExch(err, 2);
+                        units = base < nv16 ? nv16 - base : 0;
+                    }
+                    if (units) {
+                        mbar_expect_tx(&full[s], (uint32_t)units * 16);
+                        tma_load_1d(smem + (size_t)s * FLD_STAGE_BYTES, values + base * 16, (uint32_t)units * 16, &full[s]);
+                    } else {
+                        mbar_arrive(&full[s]);
+                    }
+                }
+                base += tot;
+            }
+        }
+    } else {
+        // =============================== unpack warps ======================================
+        const int t = tid & 3;
+        for (long long k = 0; k < T; ++k) {
+            const int s = (int)(k % FLD_STAGES);
+            mbar_wait(&full[s], (uint32_t)(k / FLD_STAGES) & 1u);
+            const uint32_t* vw = reinterpret_cast<const uint32_t*>(smem + (size_t)s * FLD_STAGE_BYTES);
+            uint32_t bw[FLD_ITEMS], r[FLD_ITEMS][4], g[FLD_ITEMS][5];
+#pragma unroll
+            for (int i = 0; i < FLD_ITEMS; ++i) {
+                const int fr = i * (FLD_UNPACK_THREADS / 4) + (tid >> 2);
+                const uint32_t b = meta[s].b[fr];
+                const uint32_t* w = vw + (uint32_t)meta[s].off[fr] * 4u + b * t;
+                const uint32_t q = b >> 1;
+                bw[i] = b;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) r[i][j] = w[j];
+#pragma unroll
+                for (int j = 0; j < 5; ++j) g[i][j] = w[q + j];
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&freeb[s]);  // everything this warp needs from the stage is in registers
+            uint8_t* otile = out + (size_t)(t0 + k) * FLD_TILE_BYTES;
+#pragma unroll
+            for (int i = 0; i < FLD_ITEMS; ++i) {
+                const int fr = i * (FLD_UNPACK_THREADS / 4) + (tid >> 2);
+                if (bw[i]) {
+                    const UnpackK kk = make_unpack_k(bw[i]);
+                    uint32_t a[4], cc[4];
+                    unpack32_regs(bw[i], kk, r[i], g[i], a, cc);
+                    uint4* o = reinterpret_cast<uint4*>(otile + fr * 128 + t * 32);
+                    o[0] = make_uint4(a[0], a[1], a[2], a[3]);
+                    o[1] = make_uint4(cc[0], cc[1], cc[2], cc[3]);
+                }
+            }
+        }
+    }
+    // ---- the CTA of the last range: the final partial frame ---------------------------------------
+    if (c != G - 1) return;
+    __syncthreads();
+    const uint32_t tail = (uint32_t)(n % FRAME);
+    if (tail && nframes == full_frames + 1) {
+        const uint64_t off = range_end * 16;
+        const uint32_t b = bits[full_frames];
+        const uint64_t avail = nvalues > off ? nvalues - off : 0;
+        if (b == 0 || b > 8 || ((uint64_t)tail * b + 7) / 8 > avail) {
+            if (tid == 0) atomicExch(err, 3);
+        } else {
+            decode_tail_frame(values + off, (uint32_t)(avail > 128 ? 128 : avail), tail, b, out + full_frames * FRAME);
+        }
+    }
+}
+
+// =============================================================================================
+//                                        launcher
+// =============================================================================================
+const int* fl_decode_status(const void* d_ws, size_t n)
+{
+    return reinterpret_cast<const int*>(reinterpret_cast<const uint64_t*>(d_ws) + fl_tiles(n));
+}
+
+cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_t* d_values, size_t nvalues, uint8_t* d_out,
+                             size_t n, void* d_ws, cudaStream_t stream)
+{
+    const size_t tiles = fl_tiles(n);
+    int dev = 0, sms = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    static int sm_count[64];
+    if (dev < 64 && sm_count[dev]) {
+        sms = sm_count[dev];
+    } else {
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+        if (dev < 64) sm_count[dev] = sms;
+    }
+    static const int per_sm = getenv("FLRL_FLD_CTAS") ? atoi(getenv("FLRL_FLD_CTAS")) : FLD_CTAS_PER_SM;
+    const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)sms * per_sm);
+    uint64_t* desc = reinterpret_cast<uint64_t*>(d_ws);
+    int* err = reinterpret_cast<int*>(desc + tiles);
+    e = cudaMemsetAsync(desc, 0, grid * sizeof(uint64_t), stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(err, 0, sizeof(uint64_t), stream);
+    if (e != cudaSuccess) return e;
+    constexpr int smem = FLD_STAGES * FLD_STAGE_BYTES;
+    static bool done[64];
+    if (!(dev < 64 && done[dev])) {
+        e = cudaFuncSetAttribute((const void*)fl_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        if (dev < 64) done[dev] = true;
+    }
+    fl_decode_kernel<<<grid, FLD_THREADS, smem, stream>>>(d_bits, nframes, d_values, nvalues, d_out, n, desc, err, (long long)tiles);
+    return cudaGetLastError();
+}
+
+}  // namespace flrl

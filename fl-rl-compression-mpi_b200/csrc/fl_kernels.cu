@@ -98,18 +98,6 @@ __device__ __noinline__ uint32_t encode_tail_frame(const uint8_t* in, uint32_t l
     return nbytes;
 }
 
-__device__ __noinline__ void decode_tail_frame(const uint8_t* vin, uint32_t avail, uint32_t len, uint32_t b, uint8_t* out)
-{
-    const int tid = threadIdx.x;
-    if (tid < (int)len && b >= 1 && b <= 8) {
-        const uint32_t bit = tid * b;
-        const uint32_t byte = bit >> 3, sh = bit & 7;
-        uint32_t v = byte < avail ? vin[byte] : 0u;
-        if (byte + 1 < avail) v |= (uint32_t)vin[byte + 1] << 8;
-        out[tid] = (uint8_t)((v >> sh) & ((1u << b) - 1u));
-    }
-}
-
 // =============================================================================================
 //                                         ENCODE
 // =============================================================================================
@@ -336,133 +324,6 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
 }
 
 // =============================================================================================
-//                                         DECODE
-// =============================================================================================
-// Same CTA shape: the control warp reads the tile's 128 widths (one word per lane), scans,
-// walks the look-back, and issues the TMA load of exactly the tile's value bytes; the four
-// unpack warps wait on the mbarrier, unpack into the output staging buffer, and the control
-// warp issues the TMA store.
-__global__ void __launch_bounds__(ENC_THREADS, 6)
-fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t* __restrict__ values, size_t nvalues,
-                 uint8_t* __restrict__ out, size_t n, uint64_t* __restrict__ desc, int* __restrict__ err)
-{
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* vin = smem;                      // TILE_BYTES + 128 (slack for the unpacker's over-reads)
-    uint8_t* vout = smem + TILE_BYTES + 128;  // TILE_BYTES
-    __shared__ __align__(8) uint64_t bar;
-    __shared__ TileScan sc;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const size_t full_frames = n / FRAME;
-    const long long tileno = blockIdx.x;
-    const size_t f0 = (size_t)tileno * TILE_FRAMES;
-    const int nfr = (int)(full_frames > f0 ? (full_frames - f0 < (size_t)TILE_FRAMES ? full_frames - f0 : TILE_FRAMES) : 0);
-    const bool last = tileno == (long long)gridDim.x - 1;
-
-    if (tid == THREADS) {
-        mbar_init(&bar, 1);
-        fence_mbar_init();
-    }
-    __syncthreads();
-
-    if (warp == 4) {
-        // =============================== control warp ======================================
-        uint32_t w4 = 0;
-        if (nfr == TILE_FRAMES && (reinterpret_cast<uintptr_t>(bits) & 3) == 0) {
-            w4 = reinterpret_cast<const uint32_t*>(bits + f0)[lane];
-        } else {
-            for (int k = 0; k < 4; ++k) {
-                const int f = lane * 4 + k;
-                if (f < nfr) w4 |= (uint32_t)bits[f0 + f] << (8 * k);
-            }
-        }
-        // malformed container: widths must be 1..8 (never index out of range)
-        bool bad = false;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const uint32_t b = (w4 >> (8 * k)) & 0xff;
-            if (lane * 4 + k < nfr && (b == 0 || b > 8)) bad = true;
-            if (b > 8) w4 = (w4 & ~(0xffu << (8 * k))) | (8u << (8 * k));
-        }
-        if (bad) atomicExch(err, 1);
-        reinterpret_cast<uint32_t*>(sc.b)[lane] = w4;
-        __syncwarp();
-        uint32_t total = tile_scan_widths(sc, lane);
-        uint64_t excl = 0;
-        if (tileno > 0) {
-            if (lane == 0) st_relaxed_u64(desc + tileno, LB_AGG | total);
-            excl = lookback_exclusive_sum(desc, tileno, lane);
-        }
-        if (lane == 0) {
-            st_relaxed_u64(desc + tileno, LB_INC | (excl + total));
-            if ((excl + total) * 16 > nvalues) {  // truncated values array
-                atomicExch(err, 2);
-                total = 0;
-            }
-            sc.total = total;
-            sc.base = excl;
-            if (total) {
-                mbar_expect_tx(&bar, total * 16);
-                tma_load_1d(vin, values + excl * 16, total * 16, &bar);
-            }
-        }
-        __syncwarp();
-        bar_arrive(BAR_OFFSETS, ENC_THREADS);
-        bar_sync(BAR_PACKED, ENC_THREADS);
-        if (lane == 0 && sc.total && nfr) {
-            tma_store_1d(out + f0 * FRAME, vout, (uint32_t)nfr * FRAME);
-            tma_store_commit();
-        }
-        if (!last) {
-            if (lane == 0) tma_store_wait_read<0>();
-            return;
-        }
-    } else {
-        // =============================== unpack warps ======================================
-        const int t = tid & 3;
-        bar_sync(BAR_OFFSETS, ENC_THREADS);
-        if (sc.total) {
-            mbar_wait(&bar, 0);
-            const uint32_t* vw = reinterpret_cast<const uint32_t*>(vin);
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i) {
-                const int fr = i * 32 + (tid >> 2);
-                if (fr < nfr) {
-                    const uint32_t b = sc.b[fr];
-                    const UnpackK k = make_unpack_k(b ? b : 1u);
-                    const uint32_t* w = vw + (uint32_t)sc.off[fr] * 4u + b * t;
-                    uint32_t a[4], c[4];
-                    unpack32_load(b, k, [&](uint32_t j) { return w[j]; }, a, c);
-                    if (b == 0) { a[0] = a[1] = a[2] = a[3] = 0; c[0] = c[1] = c[2] = c[3] = 0; }
-                    uint4* o = reinterpret_cast<uint4*>(vout + fr * 128 + t * 32);
-                    o[0] = make_uint4(a[0], a[1], a[2], a[3]);
-                    o[1] = make_uint4(c[0], c[1], c[2], c[3]);
-                }
-            }
-            fence_proxy_async_smem();
-        }
-        bar_arrive(BAR_PACKED, ENC_THREADS);
-        if (!last) return;
-    }
-    // ---- last tile only: the partial frame ---------------------------------------------------
-    __syncthreads();
-    {
-        const uint32_t tail = (uint32_t)(n % FRAME);
-        if (tail && nframes == full_frames + 1) {
-            const uint64_t off = (sc.base + sc.total) * 16;
-            const uint32_t b = bits[full_frames];
-            const uint64_t avail = nvalues > off ? nvalues - off : 0;
-            if (b == 0 || b > 8 || ((uint64_t)tail * b + 7) / 8 > avail) {
-                if (tid == 0) atomicExch(err, 3);
-            } else {
-                decode_tail_frame(values + off, (uint32_t)(avail > 128 ? 128 : avail), tail, b, out + full_frames * FRAME);
-            }
-        }
-    }
-    if (tid == THREADS) tma_store_wait_read<0>();
-}
-
-// =============================================================================================
 //                                        launchers
 // =============================================================================================
 size_t fl_tiles(size_t n)
@@ -480,11 +341,6 @@ extern "C" int flrl_debug_set_trace(void* d_buf)
     return (int)cudaMemcpyToSymbol(g_trace, &p, sizeof p);
 }
 #endif
-
-const int* fl_decode_status(const void* d_ws, size_t n)
-{
-    return reinterpret_cast<const int*>(reinterpret_cast<const uint64_t*>(d_ws) + fl_tiles(n));
-}
 
 // the opt-in shared-memory size is a per-device attribute: set it once per device
 static cudaError_t set_smem_once(const void* fn, int bytes, bool* done /*[64]*/)
@@ -514,22 +370,6 @@ cudaError_t fl_encode_launch(const uint8_t* d_in, size_t n, uint8_t* d_bits, uin
     if (e != cudaSuccess) return e;
     fl_encode_kernel<<<(unsigned)(tiles + lead), ENC_THREADS, smem, stream>>>(d_in, n, d_bits, d_values, d_values_size, desc,
                                                                               wdesc, (long long)tiles, lead);
-    return cudaGetLastError();
-}
-
-cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_t* d_values, size_t nvalues, uint8_t* d_out,
-                             size_t n, void* d_ws, cudaStream_t stream)
-{
-    const size_t tiles = fl_tiles(n);
-    uint64_t* desc = reinterpret_cast<uint64_t*>(d_ws);
-    int* err = reinterpret_cast<int*>(desc + tiles);
-    cudaError_t e = cudaMemsetAsync(desc, 0, (tiles + 1) * sizeof(uint64_t), stream);
-    if (e != cudaSuccess) return e;
-    constexpr int smem = 2 * TILE_BYTES + 128;
-    static bool done[64];
-    e = set_smem_once((const void*)fl_decode_kernel, smem, done);
-    if (e != cudaSuccess) return e;
-    fl_decode_kernel<<<(unsigned)tiles, ENC_THREADS, smem, stream>>>(d_bits, nframes, d_values, nvalues, d_out, n, desc, err);
     return cudaGetLastError();
 }
 

@@ -221,18 +221,23 @@ FLRL_HD void unpack16(uint64_t lo, uint64_t hi, const UnpackK& k, uint32_t x[4])
     x[2] = unpack_quad(c2, k);
     x[3] = unpack_quad(c3, k);
 }
+// The lane's words, already in registers: r0..r3 = words 0..3, g0..g4 = words q..q+4 (q = b/2) -> 32 bytes.
+FLRL_HD void unpack32_regs(uint32_t b, const UnpackK& k, const uint32_t r[4], const uint32_t g[5], uint32_t a[4], uint32_t c[4])
+{
+    const uint32_t sel = (b & 1u) ? 0x5432u : 0x3210u;
+    unpack16(((uint64_t)r[1] << 32) | r[0], ((uint64_t)r[3] << 32) | r[2], k, a);
+    uint32_t h0 = prmt(g[0], g[1], sel), h1 = prmt(g[1], g[2], sel), h2 = prmt(g[2], g[3], sel), h3 = prmt(g[3], g[4], sel);
+    unpack16(((uint64_t)h1 << 32) | h0, ((uint64_t)h3 << 32) | h2, k, c);
+}
 // The lane's b words are read through `ld(j)` (j relative to the lane's first word; the
 // callee must return 0 or anything for j >= b, never fault).  Produces 32 bytes.
 template <typename Load>
 FLRL_HD void unpack32_load(uint32_t b, const UnpackK& k, Load&& ld, uint32_t a[4], uint32_t c[4])
 {
     const uint32_t q = b >> 1;
-    const uint32_t sel = (b & 1u) ? 0x5432u : 0x3210u;
-    uint32_t r0 = ld(0u), r1 = ld(1u), r2 = ld(2u), r3 = ld(3u);
-    uint32_t g0 = ld(q), g1 = ld(q + 1), g2 = ld(q + 2), g3 = ld(q + 3), g4 = ld(q + 4);
-    unpack16(((uint64_t)r1 << 32) | r0, ((uint64_t)r3 << 32) | r2, k, a);
-    uint32_t h0 = prmt(g0, g1, sel), h1 = prmt(g1, g2, sel), h2 = prmt(g2, g3, sel), h3 = prmt(g3, g4, sel);
-    unpack16(((uint64_t)h1 << 32) | h0, ((uint64_t)h3 << 32) | h2, k, c);
+    const uint32_t r[4] = {ld(0u), ld(1u), ld(2u), ld(3u)};
+    const uint32_t g[5] = {ld(q), ld(q + 1), ld(q + 2), ld(q + 3), ld(q + 4)};
+    unpack32_regs(b, k, r, g, a, c);
 }
 
 }  // namespace flrl

@@ -90,6 +90,7 @@ struct Dev {
 };
 
 Dev g_dev[MAX_DEV];
+int g_map[MAX_DEV];  // shard index -> device ordinal for the running call (guarded by g_host_mu)
 int g_concat_peer = 0;
 std::mutex g_host_mu;  // host-layer calls share the per-device caches: one call at a time
 thread_local float tl_kernel_ms = 0, tl_total_ms = 0;
@@ -151,14 +152,34 @@ int d2h(Dev& d, void* dst, const void* src, size_t n)
     return 0;
 }
 
+// Restores the caller's current device when a host-layer call returns.
+struct DeviceGuard {
+    int dev = -1;
+    DeviceGuard() { if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); dev = -1; } }
+    ~DeviceGuard() { if (dev >= 0) cudaSetDevice(dev); }
+};
+
+// Number of GPUs the call uses and their ordinals: one GPU = the caller's CURRENT device (so a rank of a
+// multi-process job stays on its own GPU); several = devices 0 .. G-1.
 int device_count(int ngpus, int* out)
 {
     int have = 0;
     CK(cudaGetDeviceCount(&have));
     if (have <= 0) return fail((int)cudaErrorNoDevice, "CUDA Error: no CUDA device (the fl / rl methods have no CPU fallback)");
     int g = ngpus <= 0 ? have : std::min(ngpus, have);
-    *out = std::min(g, MAX_DEV);
+    g = std::min(g, MAX_DEV);
+    int cur = 0;
+    CK(cudaGetDevice(&cur));
+    for (int i = 0; i < MAX_DEV; ++i) g_map[i] = i;
+    if (g == 1) g_map[0] = cur < MAX_DEV ? cur : 0;
+    *out = g;
     return 0;
+}
+void single_gpu_map()
+{
+    int cur = 0;
+    if (cudaGetDevice(&cur) != cudaSuccess) cur = 0;
+    g_map[0] = cur < MAX_DEV ? cur : 0;
 }
 
 // contiguous 128-byte aligned shards: per = (n / (128 * G)) * 128, the last shard takes the rest
@@ -212,8 +233,8 @@ int nccl_allgather_sizes(int G)
     constexpr int ncclUint64_ = 5;  // ncclDataType_t::ncclUint64
     int rc = g_nccl.GroupStart();
     for (int g = 0; g < G && rc == 0; ++g) {
-        uint64_t* base = reinterpret_cast<uint64_t*>(g_dev[g].scal.p);
-        rc = g_nccl.AllGather(base, base + 8, 1, ncclUint64_, g_nccl.comms[G][g], g_dev[g].s);
+        uint64_t* base = reinterpret_cast<uint64_t*>(g_dev[g_map[g]].scal.p);
+        rc = g_nccl.AllGather(base, base + 8, 1, ncclUint64_, g_nccl.comms[G][g], g_dev[g_map[g]].s);
     }
     const int rc2 = g_nccl.GroupEnd();
     if (rc == 0) rc = rc2;
@@ -251,8 +272,8 @@ void collect_timing(int G)
 {
     tl_kernel_ms = tl_total_ms = 0;
     for (int g = 0; g < G; ++g) {
-        tl_kernel_ms = std::max(tl_kernel_ms, g_dev[g].kernel_ms);
-        tl_total_ms = std::max(tl_total_ms, g_dev[g].total_ms);
+        tl_kernel_ms = std::max(tl_kernel_ms, g_dev[g_map[g]].kernel_ms);
+        tl_total_ms = std::max(tl_total_ms, g_dev[g_map[g]].total_ms);
     }
 }
 
@@ -271,8 +292,8 @@ int exchange_sizes(int G, std::vector<uint64_t>& sizes)
 {
     sizes.assign(G, 0);
     if (G == 1) {
-        Dev& d = g_dev[0];
-        CK(cudaSetDevice(0));
+        Dev& d = g_dev[g_map[0]];
+        CK(cudaSetDevice(g_map[0]));
         CK(cudaMemcpyAsync(d.h_scal, d.scal.p, sizeof(uint64_t), cudaMemcpyDeviceToHost, d.s));
         CK(cudaStreamSynchronize(d.s));
         sizes[0] = d.h_scal[0];
@@ -281,18 +302,18 @@ int exchange_sizes(int G, std::vector<uint64_t>& sizes)
     if (int rc = nccl_ensure(G)) return rc;
     if (int rc = nccl_allgather_sizes(G)) return rc;
     for (int g = 0; g < G; ++g) {
-        Dev& d = g_dev[g];
-        CK(cudaSetDevice(g));
+        Dev& d = g_dev[g_map[g]];
+        CK(cudaSetDevice(g_map[g]));
         CK(cudaMemcpyAsync(d.h_scal, d.scal.p + 8 * sizeof(uint64_t), G * sizeof(uint64_t), cudaMemcpyDeviceToHost, d.s));
     }
     for (int g = 0; g < G; ++g) {
-        CK(cudaSetDevice(g));
-        CK(cudaStreamSynchronize(g_dev[g].s));
+        CK(cudaSetDevice(g_map[g]));
+        CK(cudaStreamSynchronize(g_dev[g_map[g]].s));
     }
-    for (int g = 0; g < G; ++g) sizes[g] = g_dev[0].h_scal[g];
+    for (int g = 0; g < G; ++g) sizes[g] = g_dev[g_map[0]].h_scal[g];
     for (int g = 1; g < G; ++g)  // every rank must have gathered the same vector
         for (int k = 0; k < G; ++k)
-            if (g_dev[g].h_scal[k] != sizes[k]) return fail(FLRL_E_ARG, "NCCL Error: size all-gather mismatch on GPU %d", g);
+            if (g_dev[g_map[g]].h_scal[k] != sizes[k]) return fail(FLRL_E_ARG, "NCCL Error: size all-gather mismatch on GPU %d", g);
     return 0;
 }
 
@@ -302,24 +323,24 @@ int deliver(int G, uint8_t* dst, const std::vector<const uint8_t*>& src, const s
             const std::vector<uint64_t>& len, uint64_t total)
 {
     if (G > 1 && g_concat_peer) {
-        Dev& d0 = g_dev[0];
-        CK(cudaSetDevice(0));
+        Dev& d0 = g_dev[g_map[0]];
+        CK(cudaSetDevice(g_map[0]));
         if (d0.gather.ensure(total)) return -1;
         for (int g = 0; g < G; ++g) {
             if (!len[g]) continue;
-            CK(cudaSetDevice(g));
-            CK(cudaMemcpyPeerAsync(d0.gather.p + off[g], 0, src[g], g, len[g], g_dev[g].s));
+            CK(cudaSetDevice(g_map[g]));
+            CK(cudaMemcpyPeerAsync(d0.gather.p + off[g], g_map[0], src[g], g_map[g], len[g], g_dev[g_map[g]].s));
         }
         for (int g = 0; g < G; ++g) {
-            CK(cudaSetDevice(g));
-            CK(cudaStreamSynchronize(g_dev[g].s));
+            CK(cudaSetDevice(g_map[g]));
+            CK(cudaStreamSynchronize(g_dev[g_map[g]].s));
         }
-        CK(cudaSetDevice(0));
+        CK(cudaSetDevice(g_map[0]));
         return d2h(d0, dst, d0.gather.p, total);
     }
     return for_each_gpu(G, [&](int g) -> int {
-        CK(cudaSetDevice(g));
-        return d2h(g_dev[g], dst + off[g], src[g], len[g]);
+        CK(cudaSetDevice(g_map[g]));
+        return d2h(g_dev[g_map[g]], dst + off[g], src[g], len[g]);
     });
 }
 
@@ -357,16 +378,17 @@ int flrl_fl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
     if (size == 0) return FLRL_OK;  // fl_gpu.cu:291-294
     if (!data) return fail(FLRL_E_ARG, "flrl_fl_gpu_compress: NULL input");
     std::lock_guard<std::mutex> lk(g_host_mu);
+    DeviceGuard restore;
     int G = 1;
     if (int rc = device_count(ngpus, &G)) return rc;
-    if (size < (size_t)G * 16384) G = 1;
+    if (size < (size_t)G * 16384 && G > 1) { G = 1; single_gpu_map(); }
     const size_t frames = (size + FRAME_LENGTH_ - 1) / FRAME_LENGTH_;
     if (bits_cap < frames) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_compress: bits capacity %zu < %zu", bits_cap, frames);
 
     int rc = for_each_gpu(G, [&](int g) -> int {
-        Dev& d = g_dev[g];
-        CK(cudaSetDevice(g));
-        if (d.init(g)) return -1;
+        Dev& d = g_dev[g_map[g]];
+        CK(cudaSetDevice(g_map[g]));
+        if (d.init(g_map[g])) return -1;
         size_t b0, n;
         shard_range(size, G, g, 128, &b0, &n);
         const size_t n16 = (n + 15) & ~(size_t)15;
@@ -391,15 +413,15 @@ int flrl_fl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
         total += sizes[g];
         boff[g] = b0 / 128;
         blen[g] = (n + 127) / 128;
-        vsrc[g] = g_dev[g].b.p;
-        bsrc[g] = g_dev[g].a.p;
+        vsrc[g] = g_dev[g_map[g]].b.p;
+        bsrc[g] = g_dev[g_map[g]].a.p;
     }
     if (values_cap < total) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_compress: values capacity %zu < %llu", values_cap, (unsigned long long)total);
     if ((rc = deliver(G, bits, bsrc, boff, blen, frames))) return rc;
     if ((rc = deliver(G, values, vsrc, voff, sizes, total))) return rc;
     for (int g = 0; g < G; ++g) {
-        CK(cudaSetDevice(g));
-        if (finish_timing(g_dev[g])) return -1;
+        CK(cudaSetDevice(g_map[g]));
+        if (finish_timing(g_dev[g_map[g]])) return -1;
     }
     collect_timing(G);
     *bits_size = frames;
@@ -453,15 +475,16 @@ int flrl_fl_gpu_decompress_into(size_t output_size, const uint8_t* bits, size_t 
     if (bits_size != frames) return fail(FLRL_E_FORMAT, "flrl_fl_gpu_decompress: bitsSize != ceil(outputSize/128)");
     if (out_cap < output_size) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_decompress: output capacity too small");
     std::lock_guard<std::mutex> lk(g_host_mu);
+    DeviceGuard restore;
     int G = 1;
     if (int rc = device_count(ngpus, &G)) return rc;
-    if (output_size < (size_t)G * 16384) G = 1;
+    if (output_size < (size_t)G * 16384 && G > 1) { G = 1; single_gpu_map(); }
 
     // phase A: widths of each shard to its GPU, sum of widths -> value bytes of the shard
     int rc = for_each_gpu(G, [&](int g) -> int {
-        Dev& d = g_dev[g];
-        CK(cudaSetDevice(g));
-        if (d.init(g)) return -1;
+        Dev& d = g_dev[g_map[g]];
+        CK(cudaSetDevice(g_map[g]));
+        if (d.init(g_map[g])) return -1;
         size_t b0, n;
         shard_range(output_size, G, g, 128, &b0, &n);
         const size_t nf = (n + 127) / 128;
@@ -485,8 +508,8 @@ int flrl_fl_gpu_decompress_into(size_t output_size, const uint8_t* bits, size_t 
     if (total > values_size) return fail(FLRL_E_FORMAT, "flrl_fl_gpu_decompress: values shorter than the widths imply");
     // phase B: values of each shard to its GPU, decode, output back
     rc = for_each_gpu(G, [&](int g) -> int {
-        Dev& d = g_dev[g];
-        CK(cudaSetDevice(g));
+        Dev& d = g_dev[g_map[g]];
+        CK(cudaSetDevice(g_map[g]));
         size_t b0, n;
         shard_range(output_size, G, g, 128, &b0, &n);
         const size_t nf = (n + 127) / 128;
@@ -534,13 +557,14 @@ int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
     if (size == 0) return FLRL_OK;
     if (!data || !counts || !values) return fail(FLRL_E_ARG, "flrl_rl_gpu_compress: NULL buffer");
     std::lock_guard<std::mutex> lk(g_host_mu);
+    DeviceGuard restore;
     int G = 1;
     if (int rc = device_count(ngpus, &G)) return rc;
-    if (size < (size_t)G * 16384) G = 1;
+    if (size < (size_t)G * 16384 && G > 1) { G = 1; single_gpu_map(); }
     int rc = for_each_gpu(G, [&](int g) -> int {
-        Dev& d = g_dev[g];
-        CK(cudaSetDevice(g));
-        if (d.init(g)) return -1;
+        Dev& d = g_dev[g_map[g]];
+        CK(cudaSetDevice(g_map[g]));
+        if (d.init(g_map[g])) return -1;
         size_t b0, n;
         shard_range(size, G, g, 128, &b0, &n);
         // bytes equal to the shard's first byte immediately before it: the run the shard continues
@@ -565,15 +589,15 @@ int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
     for (int g = 0; g < G; ++g) {
         off[g] = total;
         total += sizes[g];
-        csrc[g] = g_dev[g].a.p;
-        vsrc[g] = g_dev[g].b.p;
+        csrc[g] = g_dev[g_map[g]].a.p;
+        vsrc[g] = g_dev[g_map[g]].b.p;
     }
     if (pair_cap < total) return fail(FLRL_E_CAPACITY, "flrl_rl_gpu_compress: pair capacity %zu < %llu", pair_cap, (unsigned long long)total);
     if ((rc = deliver(G, counts, csrc, off, sizes, total))) return rc;
     if ((rc = deliver(G, values, vsrc, off, sizes, total))) return rc;
     for (int g = 0; g < G; ++g) {
-        CK(cudaSetDevice(g));
-        if (finish_timing(g_dev[g])) return -1;
+        CK(cudaSetDevice(g_map[g]));
+        if (finish_timing(g_dev[g_map[g]])) return -1;
     }
     collect_timing(G);
     *pairs = total;
@@ -615,14 +639,15 @@ int flrl_rl_gpu_decompress_into(const uint8_t* counts, const uint8_t* values, si
     if (pairs == 0) return FLRL_OK;
     if (!counts || !values || !out) return fail(FLRL_E_ARG, "flrl_rl_gpu_decompress: NULL buffer");
     std::lock_guard<std::mutex> lk(g_host_mu);
+    DeviceGuard restore;
     int G = 1;
     if (int rc = device_count(ngpus, &G)) return rc;
-    if (pairs < (size_t)G * 4096) G = 1;
+    if (pairs < (size_t)G * 4096 && G > 1) { G = 1; single_gpu_map(); }
     // phase A: pairs of each shard to its GPU, sum of counts -> output bytes of the shard
     int rc = for_each_gpu(G, [&](int g) -> int {
-        Dev& d = g_dev[g];
-        CK(cudaSetDevice(g));
-        if (d.init(g)) return -1;
+        Dev& d = g_dev[g_map[g]];
+        CK(cudaSetDevice(g_map[g]));
+        if (d.init(g_map[g])) return -1;
         size_t p0, np;
         shard_range(pairs, G, g, 16, &p0, &np);
         if (d.a.ensure(np + 16) || d.b.ensure(np + 16) || d.ws.ensure(rl_decode_workspace_bytes(np))) return -1;
@@ -643,8 +668,8 @@ int flrl_rl_gpu_decompress_into(const uint8_t* counts, const uint8_t* values, si
     if (total > out_cap) return fail(FLRL_E_CAPACITY, "flrl_rl_gpu_decompress: decoded size %llu exceeds the output capacity %zu",
                                      (unsigned long long)total, out_cap);
     rc = for_each_gpu(G, [&](int g) -> int {
-        Dev& d = g_dev[g];
-        CK(cudaSetDevice(g));
+        Dev& d = g_dev[g_map[g]];
+        CK(cudaSetDevice(g_map[g]));
         size_t p0, np;
         shard_range(pairs, G, g, 16, &p0, &np);
         if (d.in.ensure(olen[g] + 16)) return -1;
