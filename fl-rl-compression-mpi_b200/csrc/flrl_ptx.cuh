@@ -39,6 +39,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
 {
     while (!mbar_try_wait(bar, parity)) {
+        __nanosleep(20);  // a waiting warp must not eat the issue slots of the warps it waits for
     }
 }
 

@@ -38,7 +38,7 @@ __device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v)
 // Aggregates must be < 2^24 (the round's partial sum is kept in 32 bits).
 static constexpr int LB_W = 8;
 
-__device__ __forceinline__ uint64_t lookback_exclusive_sum(const uint64_t* desc, long long tile, int lane)
+__device__ __forceinline__ uint64_t lookback_exclusive_sum(const uint64_t* desc, long long tile, int lane, unsigned sleep_ns = 0)
 {
     uint64_t excl = 0;
     long long j0 = tile - 1 - lane;  // row k covers j0 - 32k; nearest-first order is (k, lane)
@@ -67,6 +67,7 @@ __device__ __forceinline__ uint64_t lookback_exclusive_sum(const uint64_t* desc,
                 }
             }
             if (!bad) break;
+            if (sleep_ns) __nanosleep(sleep_ns);  // back off: hundreds of warps poll the same few lines
 #pragma unroll
             for (int k = 0; k < LB_W; ++k)
                 if (k <= kstar && (v[k] >> 62) == 0) v[k] = ld_relaxed_u64(desc + (j0 - 32 * k));

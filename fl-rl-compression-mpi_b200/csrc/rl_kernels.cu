@@ -27,287 +27,10 @@
 
 namespace flrl {
 
-static constexpr int RL_THREADS = 256;
-static constexpr int RL_SEG = 32;                       // input bytes per thread
-static constexpr int RL_TILE = RL_THREADS * RL_SEG;     // 8 KiB
-static constexpr int RL_HALO = 256;                     // look-ahead: a count never exceeds 255
-static constexpr int RL_INBUF = 16 + RL_TILE + RL_HALO + 16;
-static constexpr int RL_STAGE = RL_TILE + 32;           // compacted counts / values (+ over-read slack)
-static constexpr uint64_t RL_BIAS = 255;                // run starts are stored as S + 255 >= 0
-
-// ---- run-start flags of 8 consecutive words -------------------------------------------------
-// bit (4k + j) of the result: byte j of word k differs from the byte before it.
-// high bit of each byte of t is set iff that byte of x is non-zero; the multiply gathers the
-// four (eight, for a word pair) byte flags into adjacent bits (no two partial products share
-// a bit, so there are no carries).
+// high bit of each byte of the result is set iff that byte of x is non-zero
 __device__ __forceinline__ uint32_t nz_bytes(uint32_t x)
 {
     return (((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x) & 0x80808080u;
-}
-__device__ __forceinline__ uint32_t start_mask32(const uint32_t (&w)[8], uint32_t prev_word)
-{
-    uint32_t m = 0, prev = prev_word;
-#pragma unroll
-    for (int k = 0; k < 8; k += 2) {
-        const uint32_t a = nz_bytes(w[k] ^ __byte_perm(prev, w[k], 0x6543));
-        const uint32_t b = nz_bytes(w[k + 1] ^ __byte_perm(w[k], w[k + 1], 0x6543));
-        const uint32_t g = (a >> 7) | (b >> 3);  // bit 0 / bit 4 of every byte
-        m |= ((g * 0x00204081u) >> 21 & 0xffu) << (4 * k);
-        prev = w[k + 1];
-    }
-    return m;
-}
-
-// look-back #1: start (biased) of the run that is open at the end of tile `tile - 1`.
-// d1 states: 0 not yet known, 1 "no run starts in this tile", 2 final value.
-__device__ __forceinline__ uint64_t lookback_run_start(const uint64_t* d1, long long tile, int lane)
-{
-    long long j = tile - 1 - lane;
-    while (true) {
-        const uint64_t v = (j >= 0) ? ld_relaxed_u64(d1 + j) : LB_INC;
-        const unsigned fin = __ballot_sync(0xffffffffu, (v >> 62) == 2);
-        const unsigned inv = __ballot_sync(0xffffffffu, (v >> 62) == 0);
-        if (fin) {
-            const int f = __ffs(fin) - 1;
-            if (inv & ((1u << f) - 1u)) continue;  // a nearer tile has not published yet
-            return __shfl_sync(0xffffffffu, v & LB_MASK, f);
-        }
-        if (inv) continue;
-        j -= 32;
-    }
-}
-
-// 16 staged bytes starting at byte offset u (any alignment) of a 4-byte aligned shared buffer
-__device__ __forceinline__ uint4 lds_unaligned16(const uint8_t* buf, uint32_t u)
-{
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(buf) + (u >> 2);
-    const uint32_t sel = 0x3210u + 0x1111u * (u & 3u);
-    const uint32_t a = w[0], b = w[1], c = w[2], d = w[3], e = w[4];
-    return make_uint4(__byte_perm(a, b, sel), __byte_perm(b, c, sel), __byte_perm(c, d, sel), __byte_perm(d, e, sel));
-}
-
-// cnt staged bytes -> dst[g0 .. g0 + cnt), coalesced 16-byte stores on 16-byte aligned global
-// addresses, byte stores on the two ragged ends; nothing at or past index `cap` is written.
-__device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint64_t g0, uint32_t cnt, uint64_t cap,
-                                                const uint8_t* stage, int tid)
-{
-    const uint32_t a = (uint32_t)((reinterpret_cast<uintptr_t>(dst) + g0) & 15u);
-    const uint32_t nchunks = (a + cnt + 15u) >> 4;
-    for (uint32_t q = tid; q < nchunks; q += RL_THREADS) {
-        const int u = (int)(16u * q) - (int)a;  // staging index of the chunk's first byte
-        if (u >= 0 && (uint32_t)u + 16u <= cnt && g0 + u + 16u <= cap) {
-            *reinterpret_cast<uint4*>(dst + g0 + u) = lds_unaligned16(stage, (uint32_t)u);
-        } else {
-            const int lo = u < 0 ? 0 : u;
-            const int hi = (uint32_t)u + 16u < cnt ? u + 16 : (int)cnt;
-            for (int k = lo; k < hi; ++k)
-                if (g0 + k < cap) dst[g0 + k] = stage[k];
-        }
-    }
-}
-
-// =============================================================================================
-//                                         ENCODE
-// =============================================================================================
-struct RlEncShared {
-    int wmax[8];        // per-warp last run start (tile relative), -1 none
-    uint32_t wsum[8];   // per-warp pair count
-    int wmin[8];        // per-warp first boundary position (tile relative)
-    int sentinel;       // first run start in the look-ahead halo (tile relative), or RL_TILE + RL_HALO
-    uint32_t d0;        // (tile base - start of the run entering the tile) % 255
-    uint64_t gbase;     // first pair slot of the tile
-};
-
-__global__ void __launch_bounds__(RL_THREADS, 4)
-rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, uint32_t prev_phase, int has_prev,
-                 uint8_t* __restrict__ counts, uint8_t* __restrict__ values, size_t pair_cap, uint64_t* __restrict__ d_pairs,
-                 uint64_t* __restrict__ d1, uint64_t* __restrict__ d2)
-{
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* inbuf = smem;                       // [16 left halo][tile][halo][pad]; tile byte i at inbuf[16 + i]
-    uint8_t* cnt8 = smem + RL_INBUF;             // compacted counts
-    uint8_t* val8 = cnt8 + RL_STAGE;             // compacted values
-    __shared__ __align__(8) uint64_t bar;
-    __shared__ RlEncShared sh;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long tile = blockIdx.x;
-    const size_t tbase = (size_t)tile * RL_TILE;
-    const bool last_tile = tile == (long long)gridDim.x - 1;
-
-    // ---- stage the tile: one bulk copy for the 16-byte multiple, scalar loads for the ragged end
-    const size_t lo = tile > 0 ? tbase - 16 : tbase;
-    const size_t want = tbase + RL_TILE + RL_HALO < n_avail ? tbase + RL_TILE + RL_HALO : n_avail;
-    const size_t hi16 = want & ~(size_t)15;
-    if (tid == 0) {
-        mbar_init(&bar, 1);
-        fence_mbar_init();
-        if (hi16 > lo) {
-            mbar_expect_tx(&bar, (uint32_t)(hi16 - lo));
-            tma_load_1d(inbuf + (tile > 0 ? 0 : 16), in + lo,
-                        (uint32_t)(hi16 - lo), &bar);
-        }
-    }
-    if (tid >= 32 && tid < 48) {
-        const size_t g = (hi16 > lo ? hi16 : lo) + (tid - 32);
-        if (g < want) inbuf[16 + (g - tbase)] = in[g];
-    }
-    if (tile == 0 && tid == 48) inbuf[15] = has_prev ? in[0] : (uint8_t)~in[0];
-    __syncthreads();
-    if (hi16 > lo) mbar_wait(&bar, 0);
-
-    // ---- run-start mask of this thread's 32 bytes
-    const int off = tid * RL_SEG;
-    uint32_t w[8];
-    {
-        const uint4 a = *reinterpret_cast<const uint4*>(inbuf + 16 + off);
-        const uint4 b = *reinterpret_cast<const uint4*>(inbuf + 32 + off);
-        w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
-    }
-    uint32_t m = start_mask32(w, *reinterpret_cast<const uint32_t*>(inbuf + 12 + off));
-    const size_t gpos = tbase + off;
-    // positions at or past the end of the available data close the last run; positions >= n are not emitted
-    const uint32_t k_av = n_avail > gpos ? (n_avail - gpos < 32 ? (uint32_t)(n_avail - gpos) : 32u) : 0u;
-    const uint32_t k_em = n > gpos ? (n - gpos < 32 ? (uint32_t)(n - gpos) : 32u) : 0u;
-    if (k_av < 32) m |= ~0u << k_av;
-    const uint32_t emit = k_em < 32 ? ((1u << k_em) - 1u) : ~0u;
-
-    // warp 7 also finds the first run start inside the look-ahead halo
-    if (warp == 7) {
-        int first = RL_HALO;
-        if (lane < RL_HALO / RL_SEG) {
-            const int hoff = RL_TILE + lane * RL_SEG;
-            uint32_t hw[8];
-            const uint4 a = *reinterpret_cast<const uint4*>(inbuf + 16 + hoff);
-            const uint4 b = *reinterpret_cast<const uint4*>(inbuf + 32 + hoff);
-            hw[0] = a.x; hw[1] = a.y; hw[2] = a.z; hw[3] = a.w; hw[4] = b.x; hw[5] = b.y; hw[6] = b.z; hw[7] = b.w;
-            uint32_t hm = start_mask32(hw, *reinterpret_cast<const uint32_t*>(inbuf + 12 + hoff));
-            const size_t hg = tbase + hoff;
-            const uint32_t hk = n_avail > hg ? (n_avail - hg < 32 ? (uint32_t)(n_avail - hg) : 32u) : 0u;
-            if (hk < 32) hm |= ~0u << hk;
-            if (hm) first = lane * RL_SEG + (__ffs(hm) - 1);
-        }
-        first = __reduce_min_sync(0xffffffffu, first);
-        if (lane == 0) sh.sentinel = RL_TILE + first;
-    }
-
-    // ---- S: last run start before this segment (block-wide exclusive max-scan)
-    int mine = m ? off + 31 - __clz(m) : -1;
-    int inc = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int o = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc = max(inc, o);
-    }
-    int s_rel = __shfl_up_sync(0xffffffffu, inc, 1);
-    if (lane == 0) s_rel = -1;
-    if (lane == 31) sh.wmax[warp] = inc;
-    __syncthreads();
-    {
-        int pm = -1;
-#pragma unroll
-        for (int k = 0; k < 7; ++k)
-            if (k < warp) pm = max(pm, sh.wmax[k]);
-        s_rel = max(s_rel, pm);
-    }
-    if (warp == 0) {
-        // look-back #1: only tiles whose first byte continues an earlier run need it
-        int tl = -1;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) tl = max(tl, sh.wmax[k]);
-        const bool need = (__shfl_sync(0xffffffffu, m, 0) & 1u) == 0;  // thread 0's first byte is not a run start
-        if (tl >= 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + tl + RL_BIAS));
-        if (need) {
-            uint64_t sb;  // biased start of the entering run
-            if (tile == 0) {
-                sb = RL_BIAS - prev_phase;
-            } else {
-                if (tl < 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_AGG);
-                sb = lookback_run_start(d1, tile, lane);
-            }
-            if (lane == 0) {
-                if (tl < 0) st_relaxed_u64(d1 + tile, LB_INC | sb);
-                sh.d0 = (uint32_t)((tbase + RL_BIAS - sb) % 255u);
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- the one possible 255-split inside the leading part of the segment
-    const uint32_t lead = m ? (uint32_t)(__ffs(m) - 1) : 32u;  // bytes that continue the entering run
-    uint32_t bm = m;                                           // pair boundaries: run starts + the split
-    if (lead) {
-        const uint32_t phase = s_rel >= 0 ? (uint32_t)(off - s_rel) % 255u : (sh.d0 + (uint32_t)off) % 255u;
-        const uint32_t j = phase ? 255u - phase : 0u;
-        if (j < lead) bm |= 1u << j;
-    }
-    const uint32_t e = bm & emit;
-    const uint32_t c = __popc(e);
-
-    // ---- pair slots (exclusive sum-scan) and the next boundary after this segment (suffix min)
-    uint32_t isum = c;
-    int nxt = bm ? off + (__ffs(bm) - 1) : 0x7fffffff;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t o = __shfl_up_sync(0xffffffffu, isum, d);
-        const int q = __shfl_down_sync(0xffffffffu, nxt, d);
-        if (lane >= d) isum += o;
-        if (lane + d < 32) nxt = min(nxt, q);
-    }
-    if (lane == 31) sh.wsum[warp] = isum;
-    if (lane == 0) sh.wmin[warp] = nxt;
-    int nxt_after = __shfl_down_sync(0xffffffffu, nxt, 1);
-    if (lane == 31) nxt_after = 0x7fffffff;
-    __syncthreads();
-    uint32_t slot = isum - c, total = 0;
-    {
-        nxt_after = min(nxt_after, sh.sentinel);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const uint32_t s = sh.wsum[k];
-            if (k < warp) slot += s;
-            if (k > warp) nxt_after = min(nxt_after, sh.wmin[k]);
-            total += s;
-        }
-    }
-    if (warp == 0) {
-        // look-back #2: first pair slot of the tile
-        uint64_t g = 0;
-        if (tile > 0) {
-            if (lane == 0) st_relaxed_u64(d2 + tile, LB_AGG | total);
-            g = lookback_exclusive_sum(d2, tile, lane);
-        }
-        if (lane == 0) {
-            st_relaxed_u64(d2 + tile, LB_INC | (g + total));
-            sh.gbase = g;
-            if (last_tile) *d_pairs = g + total;
-        }
-    }
-
-    // ---- compaction: (count, value) of every pair that starts in this segment
-    {
-        uint32_t bits = e, k = slot;
-        int prevb = -1;
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            val8[k] = inbuf[16 + off + b];
-            if (prevb >= 0) cnt8[k - 1] = (uint8_t)(b - prevb);
-            prevb = b;
-            ++k;
-        }
-        if (prevb >= 0) {
-            // the segment's last pair ends at the next boundary (this segment's non-emitted ones included)
-            const uint32_t later = bm & ~emit & ~((2u << prevb) - 1u);
-            const int nb = later ? off + (__ffs(later) - 1) : nxt_after;
-            const int len = nb - (off + prevb);
-            cnt8[k - 1] = (uint8_t)(len < 255 ? len : 255);
-        }
-    }
-    __syncthreads();
-    const uint64_t g0 = sh.gbase;
-    store_compacted(counts, g0, total, pair_cap, cnt8, tid);
-    store_compacted(values, g0, total, pair_cap, val8, tid);
 }
 
 // =============================================================================================
@@ -497,27 +220,11 @@ cudaError_t sum_bytes_launch(const uint8_t* d_p, size_t n, uint64_t* d_sum, cuda
 // =============================================================================================
 //                                        launchers
 // =============================================================================================
-size_t rl_encode_tiles(size_t n) { return (n + RL_TILE - 1) / RL_TILE; }
-size_t rl_encode_workspace_bytes(size_t n) { return (2 * rl_encode_tiles(n) + 2) * sizeof(uint64_t); }
 size_t rl_decode_tiles(size_t pairs) { return (pairs + RLD_PAIRS - 1) / RLD_PAIRS; }
 size_t rl_decode_workspace_bytes(size_t pairs) { return (rl_decode_tiles(pairs) + 2) * sizeof(uint64_t); }
 const int* rl_decode_status(const void* d_ws, size_t pairs)
 {
     return reinterpret_cast<const int*>(reinterpret_cast<const uint64_t*>(d_ws) + rl_decode_tiles(pairs));
-}
-
-cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint64_t prev_run, uint8_t* d_counts,
-                             uint8_t* d_values, size_t pair_cap, uint64_t* d_pairs, void* d_ws, cudaStream_t stream)
-{
-    const size_t tiles = rl_encode_tiles(n);
-    uint64_t* d1 = reinterpret_cast<uint64_t*>(d_ws);
-    uint64_t* d2 = d1 + tiles;
-    cudaError_t e = cudaMemsetAsync(d1, 0, 2 * tiles * sizeof(uint64_t), stream);
-    if (e != cudaSuccess) return e;
-    constexpr int smem = RL_INBUF + 2 * RL_STAGE;
-    rl_encode_kernel<<<(unsigned)tiles, RL_THREADS, smem, stream>>>(d_in, n, n_avail, (uint32_t)(prev_run % 255u), prev_run != 0,
-                                                                   d_counts, d_values, pair_cap, d_pairs, d1, d2);
-    return cudaGetLastError();
 }
 
 cudaError_t rl_decode_launch(const uint8_t* d_counts, const uint8_t* d_values, size_t pairs, uint8_t* d_out, size_t out_cap,
