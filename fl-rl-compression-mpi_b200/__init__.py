@@ -16,7 +16,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libflrl.so")
+LIB_PATH = os.environ.get("FLRL_LIB_PATH") or os.path.join(HERE, "libflrl.so")  # override: kernel A/B experiments
 FRAME = 128
 
 if not os.path.exists(LIB_PATH):

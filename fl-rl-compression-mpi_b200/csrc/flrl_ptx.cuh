@@ -4,6 +4,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifndef FLRL_MBAR_SLEEP
+#define FLRL_MBAR_SLEEP 20
+#endif
+
 namespace flrl {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -39,7 +43,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
 {
     while (!mbar_try_wait(bar, parity)) {
-        __nanosleep(20);  // a waiting warp must not eat the issue slots of the warps it waits for
+#if FLRL_MBAR_SLEEP
+        __nanosleep(FLRL_MBAR_SLEEP);  // a waiting warp must not eat the issue slots of the warps it waits for
+#endif
     }
 }
 

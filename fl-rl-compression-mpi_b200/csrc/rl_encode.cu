@@ -1,22 +1,21 @@
-// rl_encode.cu — run-length encoder for sm_100a: persistent CTAs, TMA input ring, deferred output.
+// rl_encode.cu — run-length encoder for sm_100a: one launch, input read once.
 //
 // The reference documents RL (IMPLEMENTATION-PLAN.md:83-152: mask -> scan -> start indices -> split of
-// runs > 255 -> emit) but ships no code.  One launch, input read once:
+// runs > 255 -> emit) but ships no code.  Structure here:
 //
-//   * grid = RLE_CTAS_PER_SM persistent CTAs per SM; CTA c takes tiles c, c + G, c + 2G, ... (8 KiB each,
-//     +16 B left halo, +256 B look-ahead), so the tiles in flight at any moment are neighbours in memory and
-//     a look-back never reaches further than one "row" of G tiles;
-//   * a control warp keeps RLE_STAGES TMA bulk loads in flight (full / free mbarriers) and runs the
-//     pair-slot look-back (#2) of tile k WHILE the 8 compute warps already work on tile k + 1;
-//   * compute warps, per tile: run-start bit mask of each 32-byte segment (XOR with the byte-shifted word,
-//     SWAR non-zero-byte test, one multiply gathers 8 flags) -> block max-scan for the start S of the run
-//     entering each segment (+ look-back #1 across tiles, depth 1 unless a whole tile is one run) -> the one
-//     possible 255-split of a segment, (i - S) % 255 == 0 (the plan's ":125" rule, replacing its iterative
-//     rescan loop) -> block sum-scan of pair counts + suffix-min of "next boundary" -> compaction of
-//     (count, value) bytes into one of two shared staging buffers;
-//   * the staged pairs of tile k are written to global memory one iteration later, when the control warp
-//     has their first slot: 16-byte stores aligned in the GLOBAL address space (unaligned shared reads are
-//     fixed up with PRMT), byte stores on the two ragged ends.
+//   * one CTA per 32 KiB tile (4 sub-tiles of 8 KiB, each its own TMA bulk load + mbarrier, so the first
+//     sub-tile is processed while the others are still in flight); 4 CTAs resident per SM;
+//   * 8 compute warps, thread = one 32-byte segment per sub-tile: run-start bit mask (XOR with the
+//     byte-shifted word, SWAR non-zero-byte test, IDP.4A gathers the byte flags into mask bits) -> nearest
+//     earlier run start S by ballot (no shuffle scan) -> the one possible 255-split of the segment,
+//     (i - S) % 255 == 0 (the plan's ":125" rule, replacing its iterative rescan loop) -> warp sum-scan of
+//     pair counts -> compaction of values and LAGGED counts (a pair's count is written when the NEXT
+//     boundary is found: no look-ahead halo, no suffix scan) into shared staging -> 16-byte stores aligned
+//     in the GLOBAL address space;
+//   * a 9th warp runs both decoupled look-backs off the compute warps' critical path: #1 = start of the
+//     run that enters the tile (gives the splits that fall before the tile's first run start, and the count
+//     of the PREVIOUS tile's last pair, which this tile writes), #2 = the tile's first pair slot;
+//   * two CTA barriers per tile; the compute warps never wait for another CTA before the store phase.
 //
 // A pair belongs to the tile (and the shard) in which it STARTS; its count looks ahead up to 255 bytes, so
 // tiles and shards concatenate to the single-stream output byte for byte.
@@ -31,39 +30,39 @@
 namespace flrl {
 
 static constexpr int RL_THREADS = 256;                  // compute threads
-static constexpr int RLE_THREADS = RL_THREADS + 32;     // + control warp
-static constexpr int RL_SEG = 32;                       // input bytes per thread
-static constexpr int RL_TILE = RL_THREADS * RL_SEG;     // 8 KiB
-static constexpr int RL_HALO = 256;                     // look-ahead: a count never exceeds 255
-static constexpr int RL_INBUF = 16 + RL_TILE + RL_HALO + 16;
-static constexpr int RL_STAGE = RL_TILE + 32;           // compacted counts / values (+ over-read slack)
-static constexpr int RLE_STAGES = 2;                    // input ring
-static constexpr int RLE_DEFER = 2;                     // a tile's pairs are stored this many iterations later
-static constexpr int RLE_NB = RLE_DEFER + 1;            // staging buffers / per-tile scratch slots
-static constexpr int RLE_CTAS_PER_SM = 3;
+static constexpr int RLE_THREADS = RL_THREADS + 32;     // + look-back warp
+static constexpr int RL_SEG = 32;                       // input bytes per thread per sub-tile
+static constexpr int RL_SUB = RL_THREADS * RL_SEG;      // 8 KiB
+static constexpr int RL_NSUB = 4;
+static constexpr int RL_TILE = RL_SUB * RL_NSUB;        // 32 KiB
+static constexpr int RL_NCHUNK = RL_NSUB * 8;           // warp chunks (1 KiB) per tile = 32
+static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][pad]
+static constexpr int RL_CAP = 11264;                    // staged pairs per round
+static constexpr int RL_STAGE = RL_CAP + 32;            // + over-read slack of the unaligned 16-byte reads
+static constexpr int RLE_CTAS_PER_SM = 4;
 static constexpr uint64_t RL_BIAS = 255;                // run starts are stored as S + 255 >= 0
-static constexpr uint32_t BAR_COMPUTE = 1;              // named barrier of the 256 compute threads
+static constexpr uint32_t BAR_ALL = 1;                  // compute warps + look-back warp
+static constexpr uint32_t BAR_COMPUTE = 2;              // compute warps only
 
-// ---- run-start flags of 8 consecutive words -------------------------------------------------
+// ---- run-start flags of 32 consecutive bytes -------------------------------------------------
 // bit (4k + j) of the result: byte j of word k differs from the byte before it.
-// nz: high bit of each byte set iff that byte is non-zero; the multiply gathers the eight byte flags of a
-// word pair into adjacent bits (no two partial products share a bit, so there are no carries).
-__device__ __forceinline__ uint32_t nz_bytes_e(uint32_t x)
+// nz_flags: 0x80 in every non-zero byte.  IDP.4A with weights 1,2,4,8 / 16,32,64,128 turns the eight byte
+// flags of a word pair into 128 * (8-bit mask); four pairs are merged with one shift and three IMADs.
+__device__ __forceinline__ uint32_t nz_flags(uint32_t x)
 {
-    return (((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x) & 0x80808080u;
+    return (((x | 0x80808080u) - 0x01010101u) | x) & 0x80808080u;
 }
 __device__ __forceinline__ uint32_t start_mask32(const uint32_t (&w)[8], uint32_t prev_word)
 {
-    uint32_t m = 0, prev = prev_word;
+    uint32_t v[4], prev = prev_word;
 #pragma unroll
     for (int k = 0; k < 8; k += 2) {
-        const uint32_t a = nz_bytes_e(w[k] ^ __byte_perm(prev, w[k], 0x6543));
-        const uint32_t b = nz_bytes_e(w[k + 1] ^ __byte_perm(w[k], w[k + 1], 0x6543));
-        const uint32_t g = (a >> 7) | (b >> 3);  // bit 0 / bit 4 of every byte
-        m |= ((g * 0x00204081u) >> 21 & 0xffu) << (4 * k);
+        const uint32_t a = nz_flags(w[k] ^ __byte_perm(prev, w[k], 0x6543));
+        const uint32_t b = nz_flags(w[k + 1] ^ __byte_perm(w[k], w[k + 1], 0x6543));
+        v[k >> 1] = __dp4a(a, 0x08040201u, __dp4a(b, 0x80402010u, 0u));
         prev = w[k + 1];
     }
-    return m;
+    return (v[0] >> 7) + v[1] * 2u + v[2] * 512u + v[3] * 131072u;
 }
 __device__ __forceinline__ uint32_t segment_mask(const uint8_t* inbuf, int off)
 {
@@ -73,22 +72,23 @@ __device__ __forceinline__ uint32_t segment_mask(const uint8_t* inbuf, int off)
     return start_mask32(w, *reinterpret_cast<const uint32_t*>(inbuf + 12 + off));
 }
 
-// look-back #1: start (biased) of the run that is open at the end of tile `tile - 1`.
+// look-back #1: biased start of the last run that begins before tile `tile`.
 // d1 states: 0 not yet known, 1 "no run starts in this tile", 2 final value.
 __device__ __forceinline__ uint64_t lookback_run_start(const uint64_t* d1, long long tile, int lane)
 {
     long long j = tile - 1 - lane;
+    uint64_t v = (j >= 0) ? ld_relaxed_u64(d1 + j) : LB_INC;
     while (true) {
-        const uint64_t v = (j >= 0) ? ld_relaxed_u64(d1 + j) : LB_INC;
         const unsigned fin = __ballot_sync(0xffffffffu, (v >> 62) == 2);
         const unsigned inv = __ballot_sync(0xffffffffu, (v >> 62) == 0);
-        if (fin) {
-            const int f = __ffs(fin) - 1;
-            if (inv & ((1u << f) - 1u)) continue;  // a nearer tile has not published yet
-            return __shfl_sync(0xffffffffu, v & LB_MASK, f);
+        const unsigned before = fin ? ((1u << (__ffs(fin) - 1)) - 1u) : 0xffffffffu;  // lanes nearer than the first final one
+        if (inv & before) {
+            if ((v >> 62) == 0) v = ld_relaxed_u64(d1 + j);  // only the lanes that saw nothing re-poll
+            continue;
         }
-        if (inv) continue;
+        if (fin) return __shfl_sync(0xffffffffu, v & LB_MASK, __ffs(fin) - 1);
         j -= 32;
+        v = (j >= 0) ? ld_relaxed_u64(d1 + j) : LB_INC;
     }
 }
 
@@ -121,305 +121,314 @@ __device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint6
     }
 }
 
-struct RlEncShared {    // per-tile scratch, double-buffered by tile parity
-    int wmax[8];        // per-warp last run start (tile relative), -1 none
-    uint32_t wsum[8];   // per-warp pair count
-    int wmin[8];        // per-warp first boundary position (tile relative)
-    int sentinel;       // first run start in the look-ahead halo (tile relative), or RL_TILE + RL_HALO
-    uint32_t d0;        // (tile base - start of the run entering the tile) % 255
-    uint32_t total;     // pairs that start in the tile (compute -> control warp)
-    uint64_t gbase;     // first pair slot of the tile (control warp -> compute)
+template <typename T>
+__device__ __forceinline__ T dmin(T a, T b) { return a < b ? a : b; }
+template <typename T>
+__device__ __forceinline__ T dmax(T a, T b) { return a > b ? a : b; }
+
+struct RlEncShared {
+    int chunk_first[RL_NCHUNK];   // first run start in each 1 KiB warp chunk (tile relative), RL_TILE if none
+    int chunk_last[RL_NCHUNK];    // last run start in each warp chunk (tile relative), -1 if none
+    uint32_t chunk_cnt[RL_NCHUNK];// boundaries in each warp chunk: low 16 bits all, high 16 bits emitted (position < n)
+    // look-back warp -> compute warps
+    uint64_t g0;                  // first pair slot of the tile
+    uint32_t nl;                  // emitted pairs that start at 255-splits before the tile's first run start
+    uint32_t lead_first;          // tile-relative position of the first such split
+    uint32_t first_start;         // tile-relative position of the tile's first run start (RL_TILE if none)
+    uint32_t nl_all;              // the same splits, emitted or not
 };
 
 __global__ void __launch_bounds__(RLE_THREADS, RLE_CTAS_PER_SM)
-rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, uint32_t prev_phase, int has_prev,
+rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_t n_scan, uint32_t prev_phase, int has_prev,
                  uint8_t* __restrict__ counts, uint8_t* __restrict__ values, size_t pair_cap, uint64_t* __restrict__ d_pairs,
-                 uint64_t* __restrict__ d1, uint64_t* __restrict__ d2, long long tiles, int dbg)
+                 uint64_t* __restrict__ d1, uint64_t* __restrict__ d2, long long tiles)
 {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* const inbufs = smem;                                // RLE_STAGES x [16 left halo][tile][halo][pad]
-    uint8_t* const stages = smem + RLE_STAGES * RL_INBUF;        // 2 x (counts, values) staging
-    __shared__ __align__(8) uint64_t full[RLE_STAGES], freeb[RLE_STAGES], agg_ready[RLE_NB], base_ready[RLE_NB];
-    __shared__ RlEncShared sh[RLE_NB];
+    uint8_t* const inbuf = smem;                       // [16 left halo][tile][pad]
+    uint8_t* const cnt8 = smem + RL_INBUF;             // staged counts
+    uint8_t* const val8 = cnt8 + RL_STAGE;             // staged values
+    __shared__ __align__(8) uint64_t full[RL_NSUB], base_ready;
+    __shared__ RlEncShared sh;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long G = gridDim.x, c = blockIdx.x;
-    const long long K = (tiles - c + G - 1) / G;  // tiles of this CTA: c, c + G, ...
+    const long long tile = blockIdx.x;
+    const size_t tbase = (size_t)tile * RL_TILE;
+    const bool last_tile = tile == tiles - 1;
+    // tile-relative limits: positions >= rel_emit are not emitted; position rel_scan is a forced boundary (the end
+    // of the data, or far enough into the look-ahead that every emitted pair has its count), nothing after it counts
+    const uint32_t rel_emit = n > tbase ? (uint32_t)dmin((size_t)(n - tbase), (size_t)RL_TILE) : 0u;
+    const uint32_t rel_scan = (uint32_t)dmin((size_t)(n_scan - tbase), (size_t)RL_TILE);  // == RL_TILE: not in this tile
+    const bool ragged = rel_emit < (uint32_t)RL_TILE || rel_scan < (uint32_t)RL_TILE;
 
     if (tid == 0) {
-        for (int s = 0; s < RLE_STAGES; ++s) {
-            mbar_init(&full[s], 1);
-            mbar_init(&freeb[s], RL_THREADS / 32);
-        }
-        for (int b = 0; b < RLE_NB; ++b) {
-            mbar_init(&agg_ready[b], 1);
-            mbar_init(&base_ready[b], 1);
-        }
+#pragma unroll
+        for (int s = 0; s < RL_NSUB; ++s) mbar_init(&full[s], 1);
+        mbar_init(&base_ready, 1);
         fence_mbar_init();
     }
     __syncthreads();
 
     if (warp == RL_THREADS / 32) {
-        // =============================== control warp ======================================
-        auto issue_load = [&](long long k) {
-            const long long tile = k * G + c;
-            const size_t tbase = (size_t)tile * RL_TILE;
-            const int s = (int)(k % RLE_STAGES);
-            uint8_t* buf = inbufs + s * RL_INBUF;
-            const size_t lo = tile > 0 ? tbase - 16 : tbase;
-            const size_t want = tbase + RL_TILE + RL_HALO < n_avail ? tbase + RL_TILE + RL_HALO : n_avail;
+        // ============================ loads, then the two look-backs ==========================
+        {
+            const size_t want = dmin((size_t)tbase + RL_TILE, n_avail);  // bytes of the tile that exist
             const size_t hi16 = want & ~(size_t)15;
+            const size_t lo0 = tile > 0 ? tbase - 16 : tbase;
             // the ragged end (< 16 bytes) and the byte "before" the stream: plain loads
             if (lane < 15) {
-                const size_t g = (hi16 > lo ? hi16 : lo) + lane;
-                if (g < want) buf[16 + (g - tbase)] = in[g];
+                const size_t g = dmax(hi16, lo0) + lane;
+                if (g < want) inbuf[16 + (g - tbase)] = in[g];
             }
-            if (tile == 0 && lane == 15) buf[15] = has_prev ? in[0] : (uint8_t)~in[0];
+            if (tile == 0 && lane == 15) inbuf[15] = has_prev ? in[0] : (uint8_t)~in[0];
             __syncwarp();
-            if (lane == 0) {
-                if (hi16 > lo) {
-                    mbar_expect_tx(&full[s], (uint32_t)(hi16 - lo));
-                    tma_load_1d(buf + (tile > 0 ? 0 : 16), in + lo, (uint32_t)(hi16 - lo), &full[s]);
+            if (lane < RL_NSUB) {
+                const size_t lo = lane == 0 ? lo0 : tbase + (size_t)lane * RL_SUB;
+                const size_t hi = dmin((size_t)tbase + (size_t)(lane + 1) * RL_SUB, hi16);
+                if (hi > lo) {
+                    mbar_expect_tx(&full[lane], (uint32_t)(hi - lo));
+                    tma_load_1d(inbuf + 16 + ((long long)lo - (long long)tbase), in + lo, (uint32_t)(hi - lo), &full[lane]);
                 } else {
-                    mbar_arrive(&full[s]);
+                    mbar_arrive(&full[lane]);
                 }
             }
-        };
-        for (long long k = 0; k < K && k < RLE_STAGES - 1; ++k) issue_load(k);
-        for (long long k = 0; k < K; ++k) {
-            const long long kn = k + RLE_STAGES - 1;
-            if (kn < K) {
-                if (kn >= RLE_STAGES) mbar_wait(&freeb[kn % RLE_STAGES], (uint32_t)(kn / RLE_STAGES - 1) & 1u);
-                issue_load(kn);
-            }
-            // look-back #2 of tile k, while the compute warps are already on tile k + 1
-            const int b = (int)(k % RLE_NB);
-            const long long tile = k * G + c;
-            mbar_wait(&agg_ready[b], (uint32_t)(k / RLE_NB) & 1u);
-            const uint32_t total = sh[b].total;
-            uint64_t g = 0;
-            if (tile > 0 && !(dbg & 2)) {
-                if (lane == 0) st_relaxed_u64(d2 + tile, LB_AGG | total);
-                g = lookback_exclusive_sum(d2, tile, lane, (unsigned)dbg >> 4);
-            } else if (dbg & 2) {
-                g = (uint64_t)tile * 100;  // TIMING EXPERIMENT ONLY: wrong slots, no look-back #2
-            }
-            if (lane == 0) {
-                st_relaxed_u64(d2 + tile, LB_INC | (g + total));
-                sh[b].gbase = g;
-                if (tile == tiles - 1) *d_pairs = g + total;
-                mbar_arrive(&base_ready[b]);
-            }
+        }
+        bar_sync(BAR_ALL, RLE_THREADS);  // #1: chunk_first / chunk_last are posted
+        const int cf = sh.chunk_first[lane], cl = sh.chunk_last[lane];
+        const int F_t = __reduce_min_sync(0xffffffffu, cf);   // first run start of the tile, RL_TILE if none
+        const int L_t = __reduce_max_sync(0xffffffffu, cl);   // last run start, -1 if none
+        uint64_t sbB = prev_phase ? RL_BIAS - prev_phase : 0;   // biased start of the run that enters the tile (< RL_BIAS)
+        if (tile > 0) {
+            if (lane == 0) st_relaxed_u64(d1 + tile, L_t >= 0 ? (LB_INC | (uint64_t)(tbase + L_t + RL_BIAS)) : LB_AGG);
+            sbB = lookback_run_start(d1, tile, lane);
+            if (L_t < 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_INC | sbB);
+        } else if (L_t >= 0 && lane == 0) {
+            st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + L_t + RL_BIAS));
+        } else if (lane == 0) {
+            st_relaxed_u64(d1 + tile, LB_INC | sbB);
+        }
+        // boundaries of the entering run: sb + 255 j.  All quantities biased by RL_BIAS so they stay non-negative.
+        const uint64_t tB = tbase + RL_BIAS;                    // biased tile base
+        const uint64_t FB = tB + (uint64_t)F_t;                 // biased first run start (or tile end)
+        const uint64_t q0 = (tB - 1 - sbB) / 255u;              // sbB < tB always (the entering run starts before the tile)
+        const uint64_t BpB = sbB + 255u * q0;                   // last boundary before the tile
+        const uint64_t limB = dmin(FB, tB + (uint64_t)rel_emit);  // emitted lead splits lie in [tB, limB)
+        const uint32_t nl_all = (uint32_t)((FB - 1 - sbB) / 255u - q0);
+        const uint32_t nl = limB > tB ? (uint32_t)((limB - 1 - sbB) / 255u - q0) : 0u;
+        const uint32_t lagged = nl_all ? 255u : (uint32_t)(FB - BpB);  // count of the last pair before this tile
+        bar_sync(BAR_ALL, RLE_THREADS);  // #2: chunk_cnt is posted
+        const uint32_t staged = __reduce_add_sync(0xffffffffu, sh.chunk_cnt[lane] >> 16);
+        const uint32_t tot = nl + staged;
+        uint64_t g = 0;
+        if (tile > 0) {
+            if (lane == 0) st_relaxed_u64(d2 + tile, LB_AGG | tot);
+            g = lookback_exclusive_sum(d2, tile, lane);
+        }
+        if (lane == 0) {
+            st_relaxed_u64(d2 + tile, LB_INC | (g + tot));
+            // the previous tile leaves its last pair's count to us when that pair is the last boundary before this
+            // tile (it cannot know where the next boundary is); a boundary at or past n is not a pair
+            if (tile > 0 && g >= 1 && g - 1 < pair_cap && BpB < n + RL_BIAS) counts[g - 1] = (uint8_t)lagged;
+            sh.g0 = g;
+            sh.nl = nl;
+            sh.lead_first = (uint32_t)(BpB + 255u - tB);
+            sh.first_start = (uint32_t)F_t;
+            sh.nl_all = nl_all;
+            if (last_tile) *d_pairs = g + tot;
+            mbar_arrive(&base_ready);
         }
         return;
     }
 
     // ================================= compute warps =======================================
-    auto store_tile = [&](long long j) {
-        const int pb = (int)(j % RLE_NB);
-        mbar_wait(&base_ready[pb], (uint32_t)(j / RLE_NB) & 1u);
-        const uint64_t g0 = sh[pb].gbase;
-        const uint32_t cnt = sh[pb].total;
-        const uint8_t* pc = stages + pb * 2 * RL_STAGE;
-        store_compacted(counts, g0, cnt, pair_cap, pc, tid);
-        store_compacted(values, g0, cnt, pair_cap, pc + RL_STAGE, tid);
-    };
-    for (long long k = 0; k < K; ++k) {
-        const int b = (int)(k % RLE_NB), s = (int)(k % RLE_STAGES);
-        const long long tile = k * G + c;
-        const size_t tbase = (size_t)tile * RL_TILE;
-        const uint8_t* inbuf = inbufs + s * RL_INBUF;
-        uint8_t* cnt8 = stages + b * 2 * RL_STAGE;
-        uint8_t* val8 = cnt8 + RL_STAGE;
-        RlEncShared& sc = sh[b];
-        mbar_wait(&full[s], (uint32_t)(k / RLE_STAGES) & 1u);
+    uint32_t bm[RL_NSUB];     // phase 1: run-start mask; phase 2 on: all pair boundaries of the segment
+    int sprev[RL_NSUB];       // phase 1: nearest earlier run start inside the warp (-1 none); phase 2 on: last boundary before the segment
+    uint32_t slot[RL_NSUB];   // first staged slot of the segment
+    const uint32_t lt_mask = (1u << lane) - 1u;
 
-        // ---- run-start mask of this thread's 32 bytes
-        const int off = tid * RL_SEG;
+    // ---- phase 1: run-start masks, nearest earlier run start by ballot
+#pragma unroll
+    for (int s = 0; s < RL_NSUB; ++s) {
+        const int off = s * RL_SUB + tid * RL_SEG;
+        mbar_wait(&full[s], 0);
         uint32_t m = segment_mask(inbuf, off);
-        const size_t gpos = tbase + off;
-        // positions at or past the end of the available data close the last run; positions >= n are not emitted
-        uint32_t emit = ~0u;
-        const bool ragged = tbase + RL_TILE + RL_HALO > n;  // CTA-uniform: only the last tiles see the end of the data
-        if (ragged) {
-            const uint32_t k_av = n_avail > gpos ? (n_avail - gpos < 32 ? (uint32_t)(n_avail - gpos) : 32u) : 0u;
-            const uint32_t k_em = n > gpos ? (n - gpos < 32 ? (uint32_t)(n - gpos) : 32u) : 0u;
-            if (k_av < 32) m |= ~0u << k_av;
-            emit = k_em < 32 ? ((1u << k_em) - 1u) : ~0u;
+        if (ragged) {  // CTA-uniform: only the last tiles see the end of the data
+            const int k = (int)rel_scan - off;
+            if (k < 0) m = 0;
+            else if (k < 32) m = (m & ((1u << k) - 1u)) | (1u << k);
         }
-
-        // warp 7 also finds the first run start inside the look-ahead halo
-        if (warp == 7) {
-            int first = RL_HALO;
-            if (lane < RL_HALO / RL_SEG) {
-                const int hoff = RL_TILE + lane * RL_SEG;
-                uint32_t hm = segment_mask(inbuf, hoff);
-                if (ragged) {
-                    const size_t hg = tbase + hoff;
-                    const uint32_t hk = n_avail > hg ? (n_avail - hg < 32 ? (uint32_t)(n_avail - hg) : 32u) : 0u;
-                    if (hk < 32) hm |= ~0u << hk;
-                }
-                if (hm) first = lane * RL_SEG + (__ffs(hm) - 1);
+        const unsigned bal = __ballot_sync(0xffffffffu, m != 0);
+        const int my_last = off + 31 - __clz(m);
+        const unsigned lower = bal & lt_mask;
+        const int S = __shfl_sync(0xffffffffu, my_last, 31 - __clz(lower | 1u));
+        sprev[s] = lower ? S : -1;
+        bm[s] = m;
+        const int wc = s * 8 + warp;
+        if (bal == 0) {
+            if (lane == 0) {
+                sh.chunk_first[wc] = RL_TILE;
+                sh.chunk_last[wc] = -1;
             }
-            first = __reduce_min_sync(0xffffffffu, first);
-            if (lane == 0) sc.sentinel = RL_TILE + first;
+        } else {
+            if (lane == __ffs(bal) - 1) sh.chunk_first[wc] = off + __ffs(m) - 1;
+            if (lane == 31 - __clz(bal)) sh.chunk_last[wc] = my_last;
         }
-
-        // ---- S: last run start before this segment (block-wide exclusive max-scan)
-        const int mine = m ? off + 31 - __clz(m) : -1;
-        int inc = mine;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int o = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc = max(inc, o);
-        }
-        int s_rel = __shfl_up_sync(0xffffffffu, inc, 1);
-        if (lane == 0) s_rel = -1;
-        if (lane == 31) sc.wmax[warp] = inc;
-        bar_sync(BAR_COMPUTE, RL_THREADS);
-        {
-            int pm = -1;
-#pragma unroll
-            for (int q = 0; q < 7; ++q)
-                if (q < warp) pm = max(pm, sc.wmax[q]);
-            s_rel = max(s_rel, pm);
-        }
-        if (warp == 0) {
-            // look-back #1: only tiles whose first byte continues an earlier run need it
-            int tl = -1;
-#pragma unroll
-            for (int q = 0; q < 8; ++q) tl = max(tl, sc.wmax[q]);
-            const bool need = (__shfl_sync(0xffffffffu, m, 0) & 1u) == 0;  // thread 0's first byte is not a run start
-            if (tl >= 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + tl + RL_BIAS));
-            if (need) {
-                uint64_t sb;  // biased start of the entering run
-                if (tile == 0) {
-                    sb = RL_BIAS - prev_phase;
-                } else if (dbg & 1) {
-                    sb = RL_BIAS;  // TIMING EXPERIMENT ONLY: wrong phase, no look-back #1
-                } else {
-                    if (tl < 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_AGG);
-                    sb = lookback_run_start(d1, tile, lane);
-                }
-                if (lane == 0) {
-                    if (tl < 0) st_relaxed_u64(d1 + tile, LB_INC | sb);
-                    sc.d0 = (uint32_t)((tbase + RL_BIAS - sb) % 255u);
-                }
-            }
-        }
-        bar_sync(BAR_COMPUTE, RL_THREADS);
-
-        // ---- the one possible 255-split inside the leading part of the segment
-        const uint32_t lead = m ? (uint32_t)(__ffs(m) - 1) : 32u;  // bytes that continue the entering run
-        uint32_t bm = m;                                           // pair boundaries: run starts + the split
-        if (lead) {
-            const uint32_t phase = s_rel >= 0 ? (uint32_t)(off - s_rel) % 255u : (sc.d0 + (uint32_t)off) % 255u;
-            const uint32_t j = phase ? 255u - phase : 0u;
-            if (j < lead) bm |= 1u << j;
-        }
-        const uint32_t e = bm & emit;
-        const uint32_t cn = __popc(e);
-
-        // ---- pair slots (exclusive sum-scan) and the next boundary after this segment (suffix min)
-        uint32_t isum = cn;
-        int nxt = bm ? off + (__ffs(bm) - 1) : 0x7fffffff;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, isum, d);
-            const int q = __shfl_down_sync(0xffffffffu, nxt, d);
-            if (lane >= d) isum += o;
-            if (lane + d < 32) nxt = min(nxt, q);
-        }
-        if (lane == 31) sc.wsum[warp] = isum;
-        if (lane == 0) sc.wmin[warp] = nxt;
-        int nxt_after = __shfl_down_sync(0xffffffffu, nxt, 1);
-        if (lane == 31) nxt_after = 0x7fffffff;
-        bar_sync(BAR_COMPUTE, RL_THREADS);
-        uint32_t slot = isum - cn, total = 0;
-        {
-            nxt_after = min(nxt_after, sc.sentinel);
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const uint32_t ws = sc.wsum[q];
-                if (q < warp) slot += ws;
-                if (q > warp) nxt_after = min(nxt_after, sc.wmin[q]);
-                total += ws;
-            }
-        }
-        if (tid == 0) {  // hand the tile's pair count to the control warp (look-back #2 runs behind our back)
-            sc.total = total;
-            mbar_arrive(&agg_ready[b]);
-        }
-
-        // ---- compaction: (count, value) of every pair that starts in this segment
-        {
-            uint32_t bits = e, kk = slot;
-            int prevb = -1;
-            while (bits) {
-                const int bi = __ffs(bits) - 1;
-                bits &= bits - 1;
-                val8[kk] = inbuf[16 + off + bi];
-                if (prevb >= 0) cnt8[kk - 1] = (uint8_t)(bi - prevb);
-                prevb = bi;
-                ++kk;
-            }
-            if (prevb >= 0) {
-                // the segment's last pair ends at the next boundary (this segment's non-emitted ones included)
-                const uint32_t later = bm & ~emit & ~((2u << prevb) - 1u);
-                const int nb = later ? off + (__ffs(later) - 1) : nxt_after;
-                const int len = nb - (off + prevb);
-                cnt8[kk - 1] = (uint8_t)(len < 255 ? len : 255);
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&freeb[s]);  // this warp is done with the input stage
-
-        // ---- deferred output of tile k - RLE_DEFER: its first slot has been resolved meanwhile
-        if (k >= RLE_DEFER) store_tile(k - RLE_DEFER);
     }
-    // ---- output of the CTA's last tiles
-    bar_sync(BAR_COMPUTE, RL_THREADS);
-    for (long long j = K > RLE_DEFER ? K - RLE_DEFER : 0; j < K; ++j) store_tile(j);
+    bar_sync(BAR_ALL, RLE_THREADS);  // #1
+
+    // ---- phase 2: the one possible 255-split of each segment, pair counts
+    {
+        const int cl = sh.chunk_last[lane];
+        const unsigned b2 = __ballot_sync(0xffffffffu, cl >= 0);
+#pragma unroll
+        for (int s = 0; s < RL_NSUB; ++s) {
+            const int off = s * RL_SUB + tid * RL_SEG;
+            const int wc = s * 8 + warp;
+            const unsigned lowerb = b2 & ((1u << wc) - 1u);
+            const int Sin = __shfl_sync(0xffffffffu, cl, 31 - __clz(lowerb | 1u));
+            int S = sprev[s];
+            if (S < 0 && lowerb) S = Sin;
+            uint32_t b = bm[s];
+            if (S >= 0) {
+                // boundaries of the entering run lie at S + 255 j; r = distance from the last one to off - 1
+                const uint32_t r = (uint32_t)(off - 1 - S) % 255u;
+                const uint32_t j = 254u - r;
+                const uint32_t lead = b ? (uint32_t)(__ffs(b) - 1) : 32u;  // bytes that continue the entering run
+                if (j < lead) b |= 1u << j;
+                sprev[s] = off - 1 - (int)r;
+            }
+            bm[s] = b;
+            uint32_t cn = __popc(b);
+            if (ragged) {
+                const int k = (int)rel_emit - off;
+                const uint32_t em = k <= 0 ? 0u : (k >= 32 ? ~0u : ((1u << k) - 1u));
+                cn |= __popc(b & em) << 16;
+            } else {
+                cn |= cn << 16;
+            }
+            uint32_t inc = cn;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            if (lane == 31) sh.chunk_cnt[wc] = inc;
+            slot[s] = (inc - cn) & 0xffffu;
+        }
+    }
+    bar_sync(BAR_ALL, RLE_THREADS);  // #2
+
+    // ---- phase 3: slots, compaction (values + lagged counts), stores
+    uint32_t total_all, total_emit;
+    {
+        const uint32_t cc = sh.chunk_cnt[lane];
+        uint32_t inc = cc;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += o;
+        }
+        const uint32_t tot = __shfl_sync(0xffffffffu, inc, 31);
+        total_all = tot & 0xffffu;
+        total_emit = tot >> 16;
+        const uint32_t excl = inc - cc;
+#pragma unroll
+        for (int s = 0; s < RL_NSUB; ++s) slot[s] += __shfl_sync(0xffffffffu, excl, s * 8 + warp) & 0xffffu;
+    }
+    const bool simple = total_all == total_emit && total_all <= (uint32_t)RL_CAP;
+    bool have_base = false;
+    uint64_t g0 = 0;
+    uint32_t nl = 0;
+    for (uint32_t w0 = 0; w0 == 0 || w0 < total_emit; w0 += RL_CAP) {
+        if (simple) {
+#pragma unroll
+            for (int s = 0; s < RL_NSUB; ++s) {
+                const int off = s * RL_SUB + tid * RL_SEG;
+                uint32_t bits = bm[s], kk = slot[s];
+                int prevpos = sprev[s];
+                while (bits) {
+                    const int pos = off + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    val8[kk] = inbuf[16 + pos];
+                    if (kk) cnt8[kk - 1] = (uint8_t)(pos - prevpos);
+                    prevpos = pos;
+                    ++kk;
+                }
+            }
+        } else {
+            if (w0) bar_sync(BAR_COMPUTE, RL_THREADS);  // the previous round's stores have read the staging buffers
+#pragma unroll
+            for (int s = 0; s < RL_NSUB; ++s) {
+                const int off = s * RL_SUB + tid * RL_SEG;
+                uint32_t bits = bm[s], kk = slot[s];
+                int prevpos = sprev[s];
+                while (bits) {
+                    const int pos = off + __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    if (kk >= w0 && kk < w0 + RL_CAP && kk < total_emit) val8[kk - w0] = inbuf[16 + pos];
+                    if (kk > w0 && kk <= w0 + RL_CAP && kk <= total_emit) cnt8[kk - 1 - w0] = (uint8_t)(pos - prevpos);
+                    prevpos = pos;
+                    ++kk;
+                }
+            }
+        }
+        bar_sync(BAR_COMPUTE, RL_THREADS);
+        if (!have_base) {
+            mbar_wait(&base_ready, 0);
+            g0 = sh.g0;
+            nl = sh.nl;
+            have_base = true;
+            // pairs that start at 255-splits of the entering run, before the tile's first run start
+            const uint32_t first_start = sh.first_start, lead_first = sh.lead_first;
+            const bool lead_lag = sh.nl_all == nl && total_all == 0;  // the last of them is the tile's last boundary
+            for (uint32_t j = tid; j < nl; j += RL_THREADS) {
+                const uint32_t p = lead_first + 255u * j;
+                const uint64_t k = g0 + j;
+                if (k < pair_cap) {
+                    values[k] = inbuf[16];
+                    // a pair that starts at the tile's last boundary gets its count from the next tile
+                    if (!(j == nl - 1 && lead_lag)) counts[k] = (uint8_t)min(255u, first_start - p);
+                }
+            }
+        }
+        if (total_emit > w0) {
+            const uint32_t cw = min((uint32_t)RL_CAP, total_emit - w0);
+            const bool tail = w0 + cw == total_emit && total_all == total_emit;  // that count is written by the next tile
+            store_compacted(values, g0 + nl + w0, cw, pair_cap, val8, tid);
+            store_compacted(counts, g0 + nl + w0, cw - (tail ? 1u : 0u), pair_cap, cnt8, tid);
+        }
+    }
 }
 
 // =============================================================================================
 //                                        launcher
 // =============================================================================================
-size_t rl_encode_tiles(size_t n) { return (n + RL_TILE - 1) / RL_TILE; }
+// positions 0 .. n_scan are scanned, n_scan = min(n_avail, n + 255) being a forced boundary
+size_t rl_encode_tiles(size_t n) { return (n + 255) / RL_TILE + 1; }
 size_t rl_encode_workspace_bytes(size_t n) { return (2 * rl_encode_tiles(n) + 2) * sizeof(uint64_t); }
 
 cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint64_t prev_run, uint8_t* d_counts,
                              uint8_t* d_values, size_t pair_cap, uint64_t* d_pairs, void* d_ws, cudaStream_t stream)
 {
-    const size_t tiles = rl_encode_tiles(n);
+    if (n == 0) return cudaMemsetAsync(d_pairs, 0, sizeof(uint64_t), stream);
+    const size_t n_scan = std::min(n_avail, n + 255);
+    const size_t tiles = n_scan / RL_TILE + 1;
     uint64_t* d1 = reinterpret_cast<uint64_t*>(d_ws);
-    uint64_t* d2 = d1 + tiles;
-    cudaError_t e = cudaMemsetAsync(d1, 0, 2 * tiles * sizeof(uint64_t), stream);
+    uint64_t* d2 = d1 + rl_encode_tiles(n);
+    cudaError_t e = cudaMemsetAsync(d1, 0, 2 * rl_encode_tiles(n) * sizeof(uint64_t), stream);
     if (e != cudaSuccess) return e;
-    constexpr int smem = RLE_STAGES * RL_INBUF + 2 * RLE_NB * RL_STAGE;
-    // the grid must be fully co-resident: CTAs wait on tiles that other CTAs of the same launch own
+    constexpr int smem = RL_INBUF + 2 * RL_STAGE;
+    static bool configured[64];
     int dev = 0;
     e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
-    static int resident[64];
-    int cap = dev < 64 ? resident[dev] : 0;
-    if (!cap) {
+    if (dev >= 64 || !configured[dev]) {
         e = cudaFuncSetAttribute((const void*)rl_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        int sms = 0, per_sm = 0;
-        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)rl_encode_kernel, RLE_THREADS, smem);
-        if (e != cudaSuccess) return e;
-        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-        static const int want = getenv("FLRL_RLE_CTAS") ? atoi(getenv("FLRL_RLE_CTAS")) : RLE_CTAS_PER_SM;
-        cap = sms * std::max(1, std::min(per_sm, want));
-        if (dev < 64) resident[dev] = cap;
+        if (dev < 64) configured[dev] = true;
     }
-    const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap);
-    rl_encode_kernel<<<grid, RLE_THREADS, smem, stream>>>(d_in, n, n_avail, (uint32_t)(prev_run % 255u), prev_run != 0, d_counts,
-                                                          d_values, pair_cap, d_pairs, d1, d2, (long long)tiles,
-                                                          getenv("FLRL_RLE_DBG") ? atoi(getenv("FLRL_RLE_DBG")) : 0);
+    // tiles are taken in blockIdx order, so every tile a CTA waits for has already started
+    rl_encode_kernel<<<(unsigned)tiles, RLE_THREADS, smem, stream>>>(d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), prev_run != 0,
+                                                                      d_counts, d_values, pair_cap, d_pairs, d1, d2, (long long)tiles);
     return cudaGetLastError();
 }
 
