@@ -3,19 +3,24 @@
 // The reference documents RL (IMPLEMENTATION-PLAN.md:83-152: mask -> scan -> start indices -> split of
 // runs > 255 -> emit) but ships no code.  Structure here:
 //
-//   * one CTA per 32 KiB tile (4 sub-tiles of 8 KiB, each its own TMA bulk load + mbarrier, so the first
-//     sub-tile is processed while the others are still in flight); 4 CTAs resident per SM;
-//   * 8 compute warps, thread = one 32-byte segment per sub-tile: run-start bit mask (XOR with the
+//   * one small CTA per 16 KiB tile, 8 CTAs resident per SM: while one CTA waits for its TMA loads or for
+//     its look-back, seven others compute (measured: persistent CTAs with an input ring were SLOWER,
+//     because every tile's look-back then waits for tiles that other CTAs process at the same moment);
+//     tiles are taken in blockIdx order, so everything a tile waits for has started earlier;
+//   * the tile arrives as four 4 KiB TMA bulk loads, each with its own mbarrier: the first sub-tile is
+//     processed while the others are still in flight;
+//   * 4 compute warps, thread = one 32-byte segment per sub-tile: run-start bit mask (XOR with the
 //     byte-shifted word, SWAR non-zero-byte test, IDP.4A gathers the byte flags into mask bits) -> nearest
 //     earlier run start S by ballot (no shuffle scan) -> the one possible 255-split of the segment,
-//     (i - S) % 255 == 0 (the plan's ":125" rule, replacing its iterative rescan loop) -> warp sum-scan of
-//     pair counts -> compaction of values and LAGGED counts (a pair's count is written when the NEXT
-//     boundary is found: no look-ahead halo, no suffix scan) into shared staging -> 16-byte stores aligned
-//     in the GLOBAL address space;
-//   * a 9th warp runs both decoupled look-backs off the compute warps' critical path: #1 = start of the
-//     run that enters the tile (gives the splits that fall before the tile's first run start, and the count
-//     of the PREVIOUS tile's last pair, which this tile writes), #2 = the tile's first pair slot;
-//   * two CTA barriers per tile; the compute warps never wait for another CTA before the store phase.
+//     (i - S) % 255 == 0 (the plan's ":125" rule, replacing its iterative rescan loop; skipped when the
+//     entering run is too short to reach 255) -> warp sum-scans of the pair counts, two sub-tiles per scan ->
+//     compaction of values and LAGGED counts (a pair's count is written when the NEXT boundary is found: no
+//     look-ahead halo, no suffix scan) into shared staging -> 16-byte stores aligned in the GLOBAL address
+//     space (unaligned shared reads fixed up with PRMT);
+//   * a 5th warp issues the loads and runs both decoupled look-backs off the compute warps' critical path:
+//     #1 = start of the run that enters the tile (gives the splits that fall before the tile's first run
+//     start, and the count of the PREVIOUS tile's last pair, which this tile writes), #2 = first pair slot;
+//   * two CTA barriers per tile; the compute warps wait for another CTA only right before the stores.
 //
 // A pair belongs to the tile (and the shard) in which it STARTS; its count looks ahead up to 255 bytes, so
 // tiles and shards concatenate to the single-stream output byte for byte.
@@ -29,20 +34,21 @@
 
 namespace flrl {
 
-static constexpr int RL_THREADS = 256;                  // compute threads
-static constexpr int RLE_THREADS = RL_THREADS + 32;     // + look-back warp
+static constexpr int RL_WARPS = 4;                      // compute warps
+static constexpr int RL_THREADS = RL_WARPS * 32;        // compute threads
+static constexpr int RLE_THREADS = RL_THREADS + 32;     // + loader / look-back warp
 static constexpr int RL_SEG = 32;                       // input bytes per thread per sub-tile
-static constexpr int RL_SUB = RL_THREADS * RL_SEG;      // 8 KiB
+static constexpr int RL_SUB = RL_THREADS * RL_SEG;      // 4 KiB
 static constexpr int RL_NSUB = 4;
-static constexpr int RL_TILE = RL_SUB * RL_NSUB;        // 32 KiB
-static constexpr int RL_NCHUNK = RL_NSUB * 8;           // warp chunks (1 KiB) per tile = 32
+static constexpr int RL_TILE = RL_SUB * RL_NSUB;        // 16 KiB
+static constexpr int RL_NCHUNK = RL_NSUB * RL_WARPS;    // warp chunks (1 KiB) per tile
 static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][pad]
-static constexpr int RL_CAP = 11264;                    // staged pairs per round
+static constexpr int RL_CAP = 4608;                     // staged pairs per round
 static constexpr int RL_STAGE = RL_CAP + 32;            // + over-read slack of the unaligned 16-byte reads
-static constexpr int RLE_CTAS_PER_SM = 4;
+static constexpr int RLE_CTAS_PER_SM = 8;
 static constexpr uint64_t RL_BIAS = 255;                // run starts are stored as S + 255 >= 0
-static constexpr uint32_t BAR_ALL = 1;                  // compute warps + look-back warp
-static constexpr uint32_t BAR_COMPUTE = 2;              // compute warps only
+static constexpr uint32_t BAR_COMPUTE = 1;              // named barrier of the compute warps
+static_assert(RL_NCHUNK <= 32 && RL_NSUB % 2 == 0, "chunk arrays are handled by one warp; sub-tiles are scanned in pairs");
 
 // ---- run-start flags of 32 consecutive bytes -------------------------------------------------
 // bit (4k + j) of the result: byte j of word k differs from the byte before it.
@@ -101,24 +107,23 @@ __device__ __forceinline__ uint4 lds_unaligned16(const uint8_t* buf, uint32_t u)
     return make_uint4(__byte_perm(a, b, sel), __byte_perm(b, c, sel), __byte_perm(c, d, sel), __byte_perm(d, e, sel));
 }
 
-// cnt staged bytes -> dst[g0 .. g0 + cnt), coalesced 16-byte stores on 16-byte aligned global
-// addresses, byte stores on the two ragged ends; nothing at or past index `cap` is written.
+// cnt staged bytes -> dst[g0 .. g0 + cnt): coalesced 16-byte stores on 16-byte aligned global addresses, the
+// (at most 15 + 15) bytes of the two ragged ends as one byte store per thread; nothing at or past index
+// `cap` is written.
 __device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint64_t g0, uint32_t cnt, uint64_t cap,
                                                 const uint8_t* stage, int tid)
 {
+    if (cap <= g0) return;
+    if (cap - g0 < cnt) cnt = (uint32_t)(cap - g0);
     const uint32_t a = (uint32_t)((reinterpret_cast<uintptr_t>(dst) + g0) & 15u);
-    const uint32_t nchunks = (a + cnt + 15u) >> 4;
-    for (uint32_t q = tid; q < nchunks; q += RL_THREADS) {
-        const int u = (int)(16u * q) - (int)a;  // staging index of the chunk's first byte
-        if (u >= 0 && (uint32_t)u + 16u <= cnt && g0 + u + 16u <= cap) {
-            *reinterpret_cast<uint4*>(dst + g0 + u) = lds_unaligned16(stage, (uint32_t)u);
-        } else {
-            const int lo = u < 0 ? 0 : u;
-            const int hi = (uint32_t)u + 16u < cnt ? u + 16 : (int)cnt;
-            for (int k = lo; k < hi; ++k)
-                if (g0 + k < cap) dst[g0 + k] = stage[k];
-        }
-    }
+    const uint32_t head = min(cnt, (16u - a) & 15u);        // bytes before the first aligned chunk
+    const uint32_t nfull = (cnt - head) >> 4;               // aligned 16-byte chunks
+    const uint32_t tail0 = head + 16u * nfull;              // staging index of the first byte after them
+    for (uint32_t q = tid; q < nfull; q += RL_THREADS)
+        *reinterpret_cast<uint4*>(dst + g0 + head + 16u * q) = lds_unaligned16(stage, head + 16u * q);
+    if ((uint32_t)tid < head) dst[g0 + tid] = stage[tid];
+    const uint32_t t2 = (uint32_t)tid - 16u;                // threads 16..31 take the tail
+    if (t2 < cnt - tail0) dst[g0 + tail0 + t2] = stage[tail0 + t2];
 }
 
 template <typename T>
@@ -126,16 +131,36 @@ __device__ __forceinline__ T dmin(T a, T b) { return a < b ? a : b; }
 template <typename T>
 __device__ __forceinline__ T dmax(T a, T b) { return a > b ? a : b; }
 
+
+
+#ifdef FLRL_TRACE
+// development aid (variant builds only): per-tile globaltimer stamps
+__device__ uint64_t* g_rle_trace = nullptr;
+__device__ __forceinline__ uint64_t gtime()
+{
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define TRACE(slot)                                                              \
+    do {                                                                         \
+        if (g_rle_trace && lane == 0) g_rle_trace[(size_t)tile * 16 + (slot)] = gtime(); \
+    } while (0)
+#else
+#define TRACE(slot) do { } while (0)
+#endif
+
 struct RlEncShared {
-    int chunk_first[RL_NCHUNK];   // first run start in each 1 KiB warp chunk (tile relative), RL_TILE if none
-    int chunk_last[RL_NCHUNK];    // last run start in each warp chunk (tile relative), -1 if none
-    uint32_t chunk_cnt[RL_NCHUNK];// boundaries in each warp chunk: low 16 bits all, high 16 bits emitted (position < n)
+    int chunk_first[RL_NCHUNK];    // first run start in each 1 KiB warp chunk (tile relative), RL_TILE if none
+    int chunk_last[RL_NCHUNK];     // last run start in each warp chunk (tile relative), -1 if none
+    uint32_t chunk_cnt[RL_NCHUNK]; // pair boundaries in each warp chunk
+    uint32_t emit_cnt[RL_WARPS];   // ragged tiles only: boundaries at positions < n, per warp
     // look-back warp -> compute warps
-    uint64_t g0;                  // first pair slot of the tile
-    uint32_t nl;                  // emitted pairs that start at 255-splits before the tile's first run start
-    uint32_t lead_first;          // tile-relative position of the first such split
-    uint32_t first_start;         // tile-relative position of the tile's first run start (RL_TILE if none)
-    uint32_t nl_all;              // the same splits, emitted or not
+    uint64_t g0;                   // first pair slot of the tile
+    uint32_t nl;                   // emitted pairs that start at 255-splits before the tile's first run start
+    uint32_t nl_all;               // the same splits, emitted or not
+    uint32_t lead_first;           // tile-relative position of the first such split
+    uint32_t first_start;          // tile-relative position of the tile's first run start (RL_TILE if none)
 };
 
 __global__ void __launch_bounds__(RLE_THREADS, RLE_CTAS_PER_SM)
@@ -147,33 +172,41 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
     uint8_t* const inbuf = smem;                       // [16 left halo][tile][pad]
     uint8_t* const cnt8 = smem + RL_INBUF;             // staged counts
     uint8_t* const val8 = cnt8 + RL_STAGE;             // staged values
-    __shared__ __align__(8) uint64_t full[RL_NSUB], base_ready;
+    __shared__ __align__(8) uint64_t full[RL_NSUB], base_ready, p1_ready, p2_ready;
     __shared__ RlEncShared sh;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long tile = blockIdx.x;
     const size_t tbase = (size_t)tile * RL_TILE;
-    const bool last_tile = tile == tiles - 1;
     // tile-relative limits: positions >= rel_emit are not emitted; position rel_scan is a forced boundary (the end
     // of the data, or far enough into the look-ahead that every emitted pair has its count), nothing after it counts
     const uint32_t rel_emit = n > tbase ? (uint32_t)dmin((size_t)(n - tbase), (size_t)RL_TILE) : 0u;
     const uint32_t rel_scan = (uint32_t)dmin((size_t)(n_scan - tbase), (size_t)RL_TILE);  // == RL_TILE: not in this tile
     const bool ragged = rel_emit < (uint32_t)RL_TILE || rel_scan < (uint32_t)RL_TILE;
 
-    if (tid == 0) {
+    if (tid == RL_THREADS) {  // the loader issues the loads before anything else happens in the CTA
 #pragma unroll
         for (int s = 0; s < RL_NSUB; ++s) mbar_init(&full[s], 1);
         mbar_init(&base_ready, 1);
+        mbar_init(&p1_ready, RL_WARPS);
+        mbar_init(&p2_ready, RL_WARPS);
         fence_mbar_init();
     }
-    __syncthreads();
-
-    if (warp == RL_THREADS / 32) {
+    if (warp == RL_WARPS) {
         // ============================ loads, then the two look-backs ==========================
         {
-            const size_t want = dmin((size_t)tbase + RL_TILE, n_avail);  // bytes of the tile that exist
+            __syncwarp();
+            const size_t want = dmin(tbase + RL_TILE, n_avail);  // end of the bytes of the tile that exist
             const size_t hi16 = want & ~(size_t)15;
             const size_t lo0 = tile > 0 ? tbase - 16 : tbase;
+            if (lane < RL_NSUB) {
+                const size_t lo = lane == 0 ? lo0 : tbase + (size_t)lane * RL_SUB;
+                const size_t hi = dmin(tbase + (size_t)(lane + 1) * RL_SUB, hi16);
+                if (hi > lo) {
+                    mbar_expect_tx(&full[lane], (uint32_t)(hi - lo));
+                    tma_load_1d(inbuf + 16 + ((long long)lo - (long long)tbase), in + lo, (uint32_t)(hi - lo), &full[lane]);
+                }
+            }
             // the ragged end (< 16 bytes) and the byte "before" the stream: plain loads
             if (lane < 15) {
                 const size_t g = dmax(hi16, lo0) + lane;
@@ -183,46 +216,42 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             __syncwarp();
             if (lane < RL_NSUB) {
                 const size_t lo = lane == 0 ? lo0 : tbase + (size_t)lane * RL_SUB;
-                const size_t hi = dmin((size_t)tbase + (size_t)(lane + 1) * RL_SUB, hi16);
-                if (hi > lo) {
-                    mbar_expect_tx(&full[lane], (uint32_t)(hi - lo));
-                    tma_load_1d(inbuf + 16 + ((long long)lo - (long long)tbase), in + lo, (uint32_t)(hi - lo), &full[lane]);
-                } else {
-                    mbar_arrive(&full[lane]);
-                }
+                const size_t hi = dmin(tbase + (size_t)(lane + 1) * RL_SUB, hi16);
+                if (!(hi > lo)) mbar_arrive(&full[lane]);
             }
         }
-        bar_sync(BAR_ALL, RLE_THREADS);  // #1: chunk_first / chunk_last are posted
-        const int cf = sh.chunk_first[lane], cl = sh.chunk_last[lane];
+        TRACE(0);
+        __syncthreads();                 // mbarriers are initialised (compute warps may now wait on them)
+        // look-back #1 starts at once: it does not depend on this tile (the compute warps publish d1[tile] themselves)
+        uint64_t sbB = prev_phase ? RL_BIAS - prev_phase : 0;   // biased start of the run that enters the tile
+        if (tile > 0) sbB = lookback_run_start(d1, tile, lane);
+        TRACE(1);
+        mbar_wait(&p1_ready, 0);  // chunk_first / chunk_last are posted
+        const int cf = lane < RL_NCHUNK ? sh.chunk_first[lane] : RL_TILE;
+        const int cl = lane < RL_NCHUNK ? sh.chunk_last[lane] : -1;
         const int F_t = __reduce_min_sync(0xffffffffu, cf);   // first run start of the tile, RL_TILE if none
         const int L_t = __reduce_max_sync(0xffffffffu, cl);   // last run start, -1 if none
-        uint64_t sbB = prev_phase ? RL_BIAS - prev_phase : 0;   // biased start of the run that enters the tile (< RL_BIAS)
-        if (tile > 0) {
-            if (lane == 0) st_relaxed_u64(d1 + tile, L_t >= 0 ? (LB_INC | (uint64_t)(tbase + L_t + RL_BIAS)) : LB_AGG);
-            sbB = lookback_run_start(d1, tile, lane);
-            if (L_t < 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_INC | sbB);
-        } else if (L_t >= 0 && lane == 0) {
-            st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + L_t + RL_BIAS));
-        } else if (lane == 0) {
-            st_relaxed_u64(d1 + tile, LB_INC | sbB);
-        }
-        // boundaries of the entering run: sb + 255 j.  All quantities biased by RL_BIAS so they stay non-negative.
-        const uint64_t tB = tbase + RL_BIAS;                    // biased tile base
+        if (L_t < 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_INC | sbB);  // no run starts here: pass the entering one on
+        TRACE(2);
+        // boundaries of the entering run: sb + 255 j.  All positions biased by RL_BIAS so they stay non-negative.
+        const uint64_t tB = tbase + RL_BIAS;                    // biased tile base; sbB < tB always
         const uint64_t FB = tB + (uint64_t)F_t;                 // biased first run start (or tile end)
-        const uint64_t q0 = (tB - 1 - sbB) / 255u;              // sbB < tB always (the entering run starts before the tile)
+        const uint64_t q0 = (tB - 1 - sbB) / 255u;
         const uint64_t BpB = sbB + 255u * q0;                   // last boundary before the tile
         const uint64_t limB = dmin(FB, tB + (uint64_t)rel_emit);  // emitted lead splits lie in [tB, limB)
         const uint32_t nl_all = (uint32_t)((FB - 1 - sbB) / 255u - q0);
         const uint32_t nl = limB > tB ? (uint32_t)((limB - 1 - sbB) / 255u - q0) : 0u;
         const uint32_t lagged = nl_all ? 255u : (uint32_t)(FB - BpB);  // count of the last pair before this tile
-        bar_sync(BAR_ALL, RLE_THREADS);  // #2: chunk_cnt is posted
-        const uint32_t staged = __reduce_add_sync(0xffffffffu, sh.chunk_cnt[lane] >> 16);
-        const uint32_t tot = nl + staged;
+        mbar_wait(&p2_ready, 0);  // chunk_cnt (and emit_cnt) are posted
+        TRACE(3);
+        const uint32_t mine = ragged ? (lane < RL_WARPS ? sh.emit_cnt[lane] : 0u) : (lane < RL_NCHUNK ? sh.chunk_cnt[lane] : 0u);
+        const uint32_t tot = nl + __reduce_add_sync(0xffffffffu, mine);
         uint64_t g = 0;
         if (tile > 0) {
             if (lane == 0) st_relaxed_u64(d2 + tile, LB_AGG | tot);
             g = lookback_exclusive_sum(d2, tile, lane);
         }
+        TRACE(4);
         if (lane == 0) {
             st_relaxed_u64(d2 + tile, LB_INC | (g + tot));
             // the previous tile leaves its last pair's count to us when that pair is the last boundary before this
@@ -230,14 +259,15 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             if (tile > 0 && g >= 1 && g - 1 < pair_cap && BpB < n + RL_BIAS) counts[g - 1] = (uint8_t)lagged;
             sh.g0 = g;
             sh.nl = nl;
+            sh.nl_all = nl_all;
             sh.lead_first = (uint32_t)(BpB + 255u - tB);
             sh.first_start = (uint32_t)F_t;
-            sh.nl_all = nl_all;
-            if (last_tile) *d_pairs = g + tot;
+            if (tile == tiles - 1) *d_pairs = g + tot;
             mbar_arrive(&base_ready);
         }
         return;
     }
+    __syncthreads();  // mbarriers are initialised
 
     // ================================= compute warps =======================================
     uint32_t bm[RL_NSUB];     // phase 1: run-start mask; phase 2 on: all pair boundaries of the segment
@@ -245,16 +275,20 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
     uint32_t slot[RL_NSUB];   // first staged slot of the segment
     const uint32_t lt_mask = (1u << lane) - 1u;
 
-    // ---- phase 1: run-start masks, nearest earlier run start by ballot
+    // ---- phase 1: run-start masks, nearest earlier run start by ballot.  The LAST sub-tile goes first: the next
+    // tile's look-back #1 only needs this tile's last run start, which is published the moment it is known
 #pragma unroll
-    for (int s = 0; s < RL_NSUB; ++s) {
+    for (int i = 0; i < RL_NSUB; ++i) {
+        const int s = (i + RL_NSUB - 1) % RL_NSUB;
         const int off = s * RL_SUB + tid * RL_SEG;
+        if (i == 0) mbar_wait(&full[s - 1], 0);  // the byte before the sub-tile's first one belongs to the previous load
         mbar_wait(&full[s], 0);
+        if (warp == 0 && i == 0) TRACE(8);
         uint32_t m = segment_mask(inbuf, off);
         if (ragged) {  // CTA-uniform: only the last tiles see the end of the data
-            const int k = (int)rel_scan - off;
-            if (k < 0) m = 0;
-            else if (k < 32) m = (m & ((1u << k) - 1u)) | (1u << k);
+            const int kk = (int)rel_scan - off;
+            if (kk < 0) m = 0;
+            else if (kk < 32) m = (m & ((1u << kk) - 1u)) | (1u << kk);
         }
         const unsigned bal = __ballot_sync(0xffffffffu, m != 0);
         const int my_last = off + 31 - __clz(m);
@@ -262,141 +296,175 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
         const int S = __shfl_sync(0xffffffffu, my_last, 31 - __clz(lower | 1u));
         sprev[s] = lower ? S : -1;
         bm[s] = m;
-        const int wc = s * 8 + warp;
-        if (bal == 0) {
-            if (lane == 0) {
-                sh.chunk_first[wc] = RL_TILE;
-                sh.chunk_last[wc] = -1;
-            }
-        } else {
-            if (lane == __ffs(bal) - 1) sh.chunk_first[wc] = off + __ffs(m) - 1;
-            if (lane == 31 - __clz(bal)) sh.chunk_last[wc] = my_last;
+        const int wc = s * RL_WARPS + warp;
+        if (m != 0 && lower == 0) sh.chunk_first[wc] = off + __ffs(m) - 1;
+        if (m != 0 && (bal >> lane) == 1u) {
+            sh.chunk_last[wc] = my_last;
+            if (wc == RL_NCHUNK - 1) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + my_last + RL_BIAS));
+        }
+        if (bal == 0 && lane == 0) {
+            sh.chunk_first[wc] = RL_TILE;
+            sh.chunk_last[wc] = -1;
         }
     }
-    bar_sync(BAR_ALL, RLE_THREADS);  // #1
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&p1_ready);
+    bar_sync(BAR_COMPUTE, RL_THREADS);  // #1
 
     // ---- phase 2: the one possible 255-split of each segment, pair counts
     {
-        const int cl = sh.chunk_last[lane];
+        const int cl = lane < RL_NCHUNK ? sh.chunk_last[lane] : -1;
         const unsigned b2 = __ballot_sync(0xffffffffu, cl >= 0);
+        if (warp == 0 && !(b2 >> (RL_NCHUNK - 1))) {
+            // the tile's last 1 KiB held no run start, so d1[tile] is still empty: last run start of the tile, or "none"
+            // (the look-back warp replaces "none" by the entering run's start once it knows it)
+            const int L_t = __reduce_max_sync(0xffffffffu, cl);
+            if (lane == 0) {
+                if (L_t >= 0) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + L_t + RL_BIAS));
+                else if (tile > 0) atomicMax(reinterpret_cast<unsigned long long*>(d1 + tile), (unsigned long long)LB_AGG);  // never undoes the look-back warp's final value
+            }
+        }
+        uint32_t cn[RL_NSUB / 2], cne = 0;
 #pragma unroll
         for (int s = 0; s < RL_NSUB; ++s) {
             const int off = s * RL_SUB + tid * RL_SEG;
-            const int wc = s * 8 + warp;
+            const int wc = s * RL_WARPS + warp;
             const unsigned lowerb = b2 & ((1u << wc) - 1u);
             const int Sin = __shfl_sync(0xffffffffu, cl, 31 - __clz(lowerb | 1u));
             int S = sprev[s];
             if (S < 0 && lowerb) S = Sin;
-            uint32_t b = bm[s];
+            uint32_t bb = bm[s];
             if (S >= 0) {
-                // boundaries of the entering run lie at S + 255 j; r = distance from the last one to off - 1
-                const uint32_t r = (uint32_t)(off - 1 - S) % 255u;
-                const uint32_t j = 254u - r;
-                const uint32_t lead = b ? (uint32_t)(__ffs(b) - 1) : 32u;  // bytes that continue the entering run
-                if (j < lead) b |= 1u << j;
-                sprev[s] = off - 1 - (int)r;
+                const uint32_t lead = bb ? (uint32_t)(__ffs(bb) - 1) : 32u;  // bytes that continue the entering run
+                if ((uint32_t)(off - S) + lead > 255u) {
+                    // boundaries of the entering run lie at S + 255 j; r = distance from the last one to off - 1
+                    const uint32_t r = (uint32_t)(off - 1 - S) % 255u;
+                    const uint32_t j = 254u - r;
+                    if (j < lead) bb |= 1u << j;
+                    S = off - 1 - (int)r;
+                }
             }
-            bm[s] = b;
-            uint32_t cn = __popc(b);
+            sprev[s] = S;  // last boundary before the segment (or -1: none in this tile)
+            bm[s] = bb;
+            if (s & 1) cn[s >> 1] |= __popc(bb) << 16;
+            else cn[s >> 1] = __popc(bb);
             if (ragged) {
-                const int k = (int)rel_emit - off;
-                const uint32_t em = k <= 0 ? 0u : (k >= 32 ? ~0u : ((1u << k) - 1u));
-                cn |= __popc(b & em) << 16;
-            } else {
-                cn |= cn << 16;
+                const int kk = (int)rel_emit - off;
+                const uint32_t em = kk <= 0 ? 0u : (kk >= 32 ? ~0u : ((1u << kk) - 1u));
+                cne += __popc(bb & em);
             }
-            uint32_t inc = cn;
+        }
+#pragma unroll
+        for (int h = 0; h < RL_NSUB / 2; ++h) {
+            uint32_t inc = cn[h];
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
                 if (lane >= d) inc += o;
             }
-            if (lane == 31) sh.chunk_cnt[wc] = inc;
-            slot[s] = (inc - cn) & 0xffffu;
+            if (lane == 31) {
+                sh.chunk_cnt[(2 * h) * RL_WARPS + warp] = inc & 0xffffu;
+                sh.chunk_cnt[(2 * h + 1) * RL_WARPS + warp] = inc >> 16;
+            }
+            const uint32_t ex = inc - cn[h];
+            slot[2 * h] = ex & 0xffffu;
+            slot[2 * h + 1] = ex >> 16;
+        }
+        if (ragged) {
+            cne = __reduce_add_sync(0xffffffffu, cne);
+            if (lane == 0) sh.emit_cnt[warp] = cne;
         }
     }
-    bar_sync(BAR_ALL, RLE_THREADS);  // #2
+    if (warp == 0) TRACE(10);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&p2_ready);
+    bar_sync(BAR_COMPUTE, RL_THREADS);  // #2
+    if (warp == 0) TRACE(11);
 
     // ---- phase 3: slots, compaction (values + lagged counts), stores
     uint32_t total_all, total_emit;
     {
-        const uint32_t cc = sh.chunk_cnt[lane];
+        const uint32_t cc = lane < RL_NCHUNK ? sh.chunk_cnt[lane] : 0u;
         uint32_t inc = cc;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
+        for (int d = 1; d < RL_NCHUNK; d <<= 1) {
             const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
             if (lane >= d) inc += o;
         }
-        const uint32_t tot = __shfl_sync(0xffffffffu, inc, 31);
-        total_all = tot & 0xffffu;
-        total_emit = tot >> 16;
+        total_all = __shfl_sync(0xffffffffu, inc, RL_NCHUNK - 1);
+        total_emit = total_all;
+        if (ragged) {
+            const uint32_t e = lane < RL_WARPS ? sh.emit_cnt[lane] : 0u;
+            total_emit = __reduce_add_sync(0xffffffffu, e);
+        }
         const uint32_t excl = inc - cc;
 #pragma unroll
-        for (int s = 0; s < RL_NSUB; ++s) slot[s] += __shfl_sync(0xffffffffu, excl, s * 8 + warp) & 0xffffu;
+        for (int s = 0; s < RL_NSUB; ++s) slot[s] += __shfl_sync(0xffffffffu, excl, s * RL_WARPS + warp);
     }
     const bool simple = total_all == total_emit && total_all <= (uint32_t)RL_CAP;
-    bool have_base = false;
-    uint64_t g0 = 0;
-    uint32_t nl = 0;
     for (uint32_t w0 = 0; w0 == 0 || w0 < total_emit; w0 += RL_CAP) {
         if (simple) {
 #pragma unroll
             for (int s = 0; s < RL_NSUB; ++s) {
                 const int off = s * RL_SUB + tid * RL_SEG;
+                const uint8_t* src = inbuf + 16 + off;
                 uint32_t bits = bm[s], kk = slot[s];
                 int prevpos = sprev[s];
                 while (bits) {
-                    const int pos = off + __ffs(bits) - 1;
+                    const int bi = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    val8[kk] = inbuf[16 + pos];
-                    if (kk) cnt8[kk - 1] = (uint8_t)(pos - prevpos);
-                    prevpos = pos;
+                    val8[kk] = src[bi];
+                    if (kk) cnt8[kk - 1] = (uint8_t)(off + bi - prevpos);
+                    prevpos = off + bi;
                     ++kk;
                 }
             }
         } else {
+            // rare: a ragged last tile, or more pairs than the staging buffers hold -> rounds
             if (w0) bar_sync(BAR_COMPUTE, RL_THREADS);  // the previous round's stores have read the staging buffers
 #pragma unroll
             for (int s = 0; s < RL_NSUB; ++s) {
                 const int off = s * RL_SUB + tid * RL_SEG;
+                const uint8_t* src = inbuf + 16 + off;
                 uint32_t bits = bm[s], kk = slot[s];
                 int prevpos = sprev[s];
                 while (bits) {
-                    const int pos = off + __ffs(bits) - 1;
+                    const int bi = __ffs(bits) - 1;
                     bits &= bits - 1;
-                    if (kk >= w0 && kk < w0 + RL_CAP && kk < total_emit) val8[kk - w0] = inbuf[16 + pos];
-                    if (kk > w0 && kk <= w0 + RL_CAP && kk <= total_emit) cnt8[kk - 1 - w0] = (uint8_t)(pos - prevpos);
-                    prevpos = pos;
+                    if (kk >= w0 && kk < w0 + RL_CAP && kk < total_emit) val8[kk - w0] = src[bi];
+                    if (kk > w0 && kk <= w0 + RL_CAP && kk <= total_emit) cnt8[kk - 1 - w0] = (uint8_t)(off + bi - prevpos);
+                    prevpos = off + bi;
                     ++kk;
                 }
             }
         }
+        if (warp == 0) TRACE(12);
         bar_sync(BAR_COMPUTE, RL_THREADS);
-        if (!have_base) {
+        if (w0 == 0) {
             mbar_wait(&base_ready, 0);
-            g0 = sh.g0;
-            nl = sh.nl;
-            have_base = true;
-            // pairs that start at 255-splits of the entering run, before the tile's first run start
-            const uint32_t first_start = sh.first_start, lead_first = sh.lead_first;
+            if (warp == 0) TRACE(13);
+            // pairs that start at 255-splits of the entering run, before the tile's first run start (long runs only)
+            const uint32_t nl = sh.nl;
             const bool lead_lag = sh.nl_all == nl && total_all == 0;  // the last of them is the tile's last boundary
             for (uint32_t j = tid; j < nl; j += RL_THREADS) {
-                const uint32_t p = lead_first + 255u * j;
-                const uint64_t k = g0 + j;
+                const uint32_t p = sh.lead_first + 255u * j;
+                const uint64_t k = sh.g0 + j;
                 if (k < pair_cap) {
                     values[k] = inbuf[16];
                     // a pair that starts at the tile's last boundary gets its count from the next tile
-                    if (!(j == nl - 1 && lead_lag)) counts[k] = (uint8_t)min(255u, first_start - p);
+                    if (!(j == nl - 1 && lead_lag)) counts[k] = (uint8_t)min(255u, sh.first_start - p);
                 }
             }
         }
         if (total_emit > w0) {
             const uint32_t cw = min((uint32_t)RL_CAP, total_emit - w0);
             const bool tail = w0 + cw == total_emit && total_all == total_emit;  // that count is written by the next tile
-            store_compacted(values, g0 + nl + w0, cw, pair_cap, val8, tid);
-            store_compacted(counts, g0 + nl + w0, cw - (tail ? 1u : 0u), pair_cap, cnt8, tid);
+            const uint64_t g0 = sh.g0 + sh.nl + w0;
+            store_compacted(values, g0, cw, pair_cap, val8, tid);
+            store_compacted(counts, g0, cw - (tail ? 1u : 0u), pair_cap, cnt8, tid);
         }
     }
+    if (warp == 0) TRACE(14);
 }
 
 // =============================================================================================
@@ -433,3 +501,10 @@ cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint
 }
 
 }  // namespace flrl
+
+#ifdef FLRL_TRACE
+extern "C" int flrl_debug_set_rle_trace(void* d_buf)
+{
+    return (int)cudaMemcpyToSymbol(flrl::g_rle_trace, &d_buf, sizeof(d_buf));
+}
+#endif
