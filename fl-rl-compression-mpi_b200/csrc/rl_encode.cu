@@ -44,10 +44,16 @@ static constexpr int RL_NSUB = 4;
 static constexpr int RL_TILE = RL_SUB * RL_NSUB;        // 16 KiB
 static constexpr int RL_NCHUNK = RL_NSUB * RL_WARPS;    // warp chunks (1 KiB) per tile
 static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][pad]
-static constexpr int RL_RING = 8192;                    // staged pairs (power of two)
+#ifndef RL_RING_PAIRS
+#define RL_RING_PAIRS 8192
+#endif
+#ifndef RLE_CTAS
+#define RLE_CTAS 6
+#endif
+static constexpr int RL_RING = RL_RING_PAIRS;           // staged pairs (power of two)
 static constexpr int RL_RINGB = RL_RING + 32;           // + over-read slack of the unaligned 16-byte reads
 static constexpr int RLE_Q = 32;                        // tiles of one CTA that may wait for their first slot
-static constexpr int RLE_CTAS_PER_SM = 6;
+static constexpr int RLE_CTAS_PER_SM = RLE_CTAS;
 static constexpr uint64_t RL_BIAS = 255;                // run starts are stored as S + 255 >= 0
 static constexpr uint32_t BAR_COMPUTE = 1;              // named barrier of the compute warps
 static_assert(RL_NCHUNK <= 32 && RL_NSUB % 2 == 0, "chunk arrays are handled by one warp; sub-tiles are scanned in pairs");
@@ -162,36 +168,79 @@ __device__ __forceinline__ uint64_t gtime()
 
 // The scanner (one warp of the grid's first CTA): exclusive prefix sum of the tiles' pair counts, in tile order.
 // agg[t] = 0x80000000 | pairs of tile t (0 = not yet posted); inc[t] = 1 << 63 | first slot of tile t.
-// 512 counts are loaded with all loads in flight; only entries that were still empty are polled again.
-static constexpr int RLE_SCAN_PER_LANE = 16;
+// A lane owns 8 consecutive tiles (two 16-byte loads, a serial prefix, four 32-byte... eight 8-byte results written
+// as 16-byte stores), the warp 256; the next 256 counts are already in flight while the current ones are
+// summed, and only the loads that still held an empty entry are repeated.  It must run several times faster
+// than the tiles arrive: whenever it has waited for a straggler, everything behind that tile waits with it.
+struct ScanRegs {
+    uint4 a, b;
+};
+__device__ __forceinline__ uint4 ld_relaxed_u32x4(const uint32_t* p)
+{
+    uint4 v;
+    asm volatile("ld.relaxed.gpu.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64x2(uint64_t* p, uint64_t x, uint64_t y)
+{
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(x), "l"(y) : "memory");
+}
+__device__ __forceinline__ bool all_posted(const uint4& v) { return ((v.x & v.y & v.z & v.w) >> 31) != 0; }
 __device__ __forceinline__ void scan_pair_counts(const uint32_t* __restrict__ agg, uint64_t* __restrict__ inc, long long tiles, int lane)
 {
+    // the arrays are padded to a multiple of 256 entries (rl_encode_tiles), so whole chunks can be read and written;
+    // entries at or past `tiles` are never posted and count as 0
     uint64_t base = 0;
-    for (long long r0 = 0; r0 < tiles; r0 += 32 * RLE_SCAN_PER_LANE) {
-        const long long r1 = r0 + 32 * RLE_SCAN_PER_LANE < tiles ? r0 + 32 * RLE_SCAN_PER_LANE : tiles;
-        uint32_t v[RLE_SCAN_PER_LANE];
-#pragma unroll
-        for (int j = 0; j < RLE_SCAN_PER_LANE; ++j) {
-            const long long t = r0 + 32 * j + lane;
-            v[j] = t < r1 ? ld_relaxed_u32(agg + t) : 0x80000000u;
+    const long long chunks = (tiles + 255) / 256;
+    ScanRegs cur, nxt;
+    cur.a = ld_relaxed_u32x4(agg + 8 * lane);
+    cur.b = ld_relaxed_u32x4(agg + 8 * lane + 4);
+    for (long long c = 0; c < chunks; ++c) {
+        const long long t0 = c * 256 + 8 * lane;
+        if (c + 1 < chunks) {
+            nxt.a = ld_relaxed_u32x4(agg + t0 + 256);
+            nxt.b = ld_relaxed_u32x4(agg + t0 + 260);
         }
-#pragma unroll
-        for (int j = 0; j < RLE_SCAN_PER_LANE; ++j) {
-            const long long t = r0 + 32 * j + lane;
-            if (r0 + 32 * j >= r1) break;
-            while (__any_sync(0xffffffffu, (v[j] >> 31) == 0)) {
-                if ((v[j] >> 31) == 0) v[j] = ld_relaxed_u32(agg + t);
+        const bool real_a = t0 + 4 <= tiles, real_b = t0 + 8 <= tiles;  // groups that hold only real tiles
+        while (true) {
+            // a group that reaches past the last tile is checked entry by entry
+            bool ok = true;
+            if (real_a) ok = all_posted(cur.a);
+            else {
+                if (t0 + 0 < tiles) ok = ok && (cur.a.x >> 31);
+                if (t0 + 1 < tiles) ok = ok && (cur.a.y >> 31);
+                if (t0 + 2 < tiles) ok = ok && (cur.a.z >> 31);
             }
-            const uint32_t a = v[j] & 0x7fffffffu;
-            uint32_t s = a;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t o = __shfl_up_sync(0xffffffffu, s, d);
-                if (lane >= d) s += o;
+            bool okb = true;
+            if (real_b) okb = all_posted(cur.b);
+            else {
+                if (t0 + 4 < tiles) okb = okb && (cur.b.x >> 31);
+                if (t0 + 5 < tiles) okb = okb && (cur.b.y >> 31);
+                if (t0 + 6 < tiles) okb = okb && (cur.b.z >> 31);
             }
-            if (t < r1) st_relaxed_u64(inc + t, (1ull << 63) | (base + s - a));
-            base += __shfl_sync(0xffffffffu, s, 31);
+            if (!__any_sync(0xffffffffu, !(ok && okb))) break;
+            if (!ok) cur.a = ld_relaxed_u32x4(agg + t0);
+            if (!okb) cur.b = ld_relaxed_u32x4(agg + t0 + 4);
         }
+        uint32_t v[8] = {cur.a.x, cur.a.y, cur.a.z, cur.a.w, cur.b.x, cur.b.y, cur.b.z, cur.b.w};
+        uint32_t ex[8], run = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            ex[j] = run;
+            run += (t0 + j < tiles) ? (v[j] & 0x7fffffffu) : 0u;
+        }
+        uint32_t s = run;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, s, d);
+            if (lane >= d) s += o;
+        }
+        const uint64_t lb = base + (s - run);
+#pragma unroll
+        for (int j = 0; j < 8; j += 2)
+            st_relaxed_u64x2(inc + t0 + j, (1ull << 63) | (lb + ex[j]), (1ull << 63) | (lb + ex[j + 1]));
+        base += __shfl_sync(0xffffffffu, s, 31);
+        cur = nxt;
     }
 }
 
@@ -377,6 +426,9 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             if (lane < rr) {
                 g &= ~(1ull << 63);
                 e.g0 = g;
+#ifdef FLRL_TRACE
+                if (g_rle_trace) g_rle_trace[(size_t)e.tile * 16 + 5] = gtime();
+#endif
                 if (e.lagged && g >= 1 && g - 1 < pair_cap) counts[g - 1] = (uint8_t)e.lagged;
                 if (e.tile == tiles - 1) *d_pairs = g + e.tot;
             }
@@ -436,8 +488,8 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             const uint32_t upto = wait_ready(n_stored + 1u);
             for (; n_stored < upto; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
         }
-        mbar_wait(&full[RL_NSUB - 2], par);
-        mbar_wait(&full[RL_NSUB - 1], par);
+#pragma unroll
+        for (int s = 0; s < RL_NSUB; ++s) mbar_wait(&full[s], par);  // the whole tile: the four mask computations below interleave
         const long long tile = *reinterpret_cast<const volatile long long*>(&sh.cur_tile);
         if (tile < 0) break;
         const size_t tbase = (size_t)tile * RL_TILE;
@@ -458,7 +510,6 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
         for (int i = 0; i < RL_NSUB; ++i) {
             const int s = (i + RL_NSUB - 1) % RL_NSUB;
             const int off = s * RL_SUB + tid * RL_SEG;
-            mbar_wait(&full[s], par);  // (the byte before sub-tile 3 belongs to load 2: waited for above)
             uint32_t m = segment_mask(inbuf, off);
             if (ragged) {  // CTA-uniform: only the last tiles see the end of the data
                 const int kk = (int)rel_scan - off;
@@ -676,7 +727,7 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
 //                                        launcher
 // =============================================================================================
 // positions 0 .. n_scan are scanned, n_scan = min(n_avail, n + 255) being a forced boundary
-size_t rl_encode_tiles(size_t n) { return (n + 255) / RL_TILE + 1; }
+size_t rl_encode_tiles(size_t n) { return (((n + 255) / RL_TILE + 1) + 255) / 256 * 256; }  // padded: the scanner works on whole chunks
 size_t rl_encode_workspace_bytes(size_t n) { return (3 * rl_encode_tiles(n) + 2) * sizeof(uint64_t); }
 
 cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint64_t prev_run, uint8_t* d_counts,

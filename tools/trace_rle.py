@@ -26,10 +26,10 @@ assert flrl.lib.flrl_debug_set_rle_trace(buf.data_ptr()) == 0
 enc.launch(d)
 torch.cuda.synchronize()
 t = buf.reshape(tiles, 16)[1000:60000].double()
-names = {0: "lb:loads issued", 8: "c: first data", 9: "c: phase1 done", 1: "lb: bar1 passed", 2: "lb: LB#1 done", 10: "c: phase2 done",
-         11: "c: bar2 passed", 3: "lb: bar2 passed", 12: "c: compaction done", 4: "lb: LB#2 done", 13: "c: base seen", 14: "c: end"}
+names = {0: "sv: loads issued", 8: "c: first data", 9: "c: phase1 done", 1: "sv: LB#1 done", 10: "c: phase2 done",
+         3: "sv: p2 seen", 12: "c: compaction done", 14: "c: tile done (+drain)", 5: "base: slot known"}
 t0 = t[:, 0]
-for k in (0, 8, 9, 1, 2, 10, 11, 3, 12, 4, 13, 14):
+for k in (0, 8, 9, 1, 10, 3, 12, 14, 5):
     dt = (t[:, k] - t0) / 1000.0
     print(f"{names[k]:22s} mean {dt.mean().item():7.2f} us  p10 {dt.quantile(0.1).item():7.2f}  p90 {dt.quantile(0.9).item():7.2f}")
 starts = torch.sort(t0).values
