@@ -9,10 +9,10 @@
 //     malformed and flagged) posted to the grid's scanner warp (rl_scan.cuh), which answers with the tile's first
 //     output byte.  By the time the compute warps reach the tile, that answer is normally there: no tile
 //     waits for a look-back;
-//   * 8 compute warps: block scan of the counts -> exclusive starts in shared memory (":164-171") + for long
-//     runs a table "pair that covers output byte 256 b" -> every thread owns 16-byte chunks aligned in the
+//   * 8 compute warps: block scan of the counts -> exclusive starts in shared memory (":164-171") + a table
+//     "pair that covers output byte b << sh" -> every thread owns 16-byte chunks aligned in the
 //     OUTPUT address space, finds the covering pair by a binary search (":172-179") that the table narrows to the
-//     pairs of one 256-byte block (1-2 steps on long runs instead of 12), and XORs value deltas into two
+//     pairs of one block (0-1 steps instead of 12), and XORs value deltas into two
 //     64-bit words -> coalesced 128-bit stores.
 #include <stdlib.h>
 
@@ -37,7 +37,6 @@ static constexpr int RLD_PER = 16;                          // pairs per thread
 static constexpr int RLD_PAIRS = RLD_THREADS * RLD_PER;     // 4096 pairs per tile (<= 1,044,480 output bytes)
 static constexpr int RLD_SLOTS = RLD_SLOTS_N;               // tiles the service warp may be ahead
 static constexpr int RLD_CTAS_PER_SM = RLD_CTAS;
-static constexpr uint32_t RLD_TBL_MIN = 16u * RLD_PAIRS;    // build the block table when the mean count is >= 16
 static constexpr uint32_t BAR_D = 1;                        // named barrier of the compute warps
 
 // high bit of each byte of the result is set iff that byte of x is non-zero
@@ -158,7 +157,10 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
         const uint32_t np = meta[s].np, total = meta[s].total;
         const uint8_t* cnt = slots + s * 2 * RLD_PAIRS;
         const uint8_t* val = cnt + RLD_PAIRS;
-        const bool use_tbl = total >= RLD_TBL_MIN;
+        // block table: tbl[b] = pair that covers output byte b << sh of the tile; the block size is the smallest power of
+        // two >= 16 for which the table has at most 4096 entries, so a block holds about one pair on long runs
+        // and is a single 16-byte chunk on short ones (no search at all)
+        const uint32_t sh = total <= 16u * RLD_PAIRS ? 4u : 32u - (uint32_t)__clz((total - 1u) >> 12);
 
         // ---- scan of the counts: 16 per thread
         uint32_t c[4];
@@ -201,10 +203,7 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
             for (int j = 0; j < 16; ++j) {
                 o[j] = run;
                 const uint32_t cj = (c[j >> 2] >> (8 * (j & 3))) & 0xffu;
-                if (use_tbl && cj) {
-                    const uint32_t b = (run + 255u) >> 8;  // the one 256-byte boundary a pair can cover
-                    if ((b << 8) < run + cj) tbl[b] = (uint16_t)(tid * RLD_PER + j);
-                }
+                for (uint32_t b = (run + (1u << sh) - 1u) >> sh; (b << sh) < run + cj; ++b) tbl[b] = (uint16_t)(tid * RLD_PER + j);
                 run += cj;
             }
             uint4* dst = reinterpret_cast<uint4*>(offs + tid * RLD_PER);
@@ -228,10 +227,10 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
             const uint32_t hi = (uint32_t)(p + 16) < tot ? (uint32_t)(p + 16) : tot;
             // j = last pair with offs[j] <= lo  (IMPLEMENTATION-PLAN.md:164-179, binary search)
             uint32_t a = 0, b = np;  // invariant: offs[a] <= lo, offs[b] > lo (offs[np] = total > lo)
-            if (use_tbl) {
-                const uint32_t blk = lo >> 8;
+            {
+                const uint32_t blk = lo >> sh;
                 a = tbl[blk];
-                if (((blk + 1u) << 8) < total) b = (uint32_t)tbl[blk + 1u] + 1u;
+                if (((blk + 1u) << sh) < total) b = (uint32_t)tbl[blk + 1u] + 1u;
             }
             while (b - a > 1) {
                 const uint32_t mid = (a + b) >> 1;
