@@ -384,7 +384,7 @@ def run_ours(args):
                    "compress_frac_of_hbm": round(work.alg_bytes / enc_ms / 1e6 / peak, 4),
                    "decompress_frac_of_hbm": round(work.alg_bytes / dec_ms / 1e6 / peak, 4)},
         "roofline": {"bound": "hbm", "kernel": work.kernels[slow], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": TRAFFIC.get(work.kernels[slow]),
+                     "frac": round(achieved / peak, 4), "traffic": TRAFFIC.get((args.workload, work.kernels[slow])) if n == GIB else None,
                      "algorithmic_bytes": int(work.alg_bytes), "launch_ms": round(k_ms, 4), "peak_source": peak_src},
         "e2e": e2e,
         "gpu_launches": 2 * args.steps,
@@ -397,8 +397,14 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures (profiles/)
-TRAFFIC = {}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) from the committed `ncu --set full` captures
+# (profiles/r01_run5_*_ncu_full.csv; 1 GiB per launch, the bench's default size)
+TRAFFIC = {
+    ("fl", "fl_encode_kernel"): 1_640_366_000, ("fl", "fl_decode_kernel"): 1_641_514_000,
+    ("rl4", "rl_encode_kernel"): 1_579_041_000, ("rl4", "rl_decode_kernel"): 1_553_995_000,
+    ("rl64", "rl_encode_kernel"): 1_110_635_000, ("rl64", "rl_decode_kernel"): 1_049_531_000,
+    ("rl4096", "rl_encode_kernel"): 1_088_694_000, ("rl4096", "rl_decode_kernel"): 1_024_660_000,
+}
 
 
 # ------------------------------------------------------- CPU baseline / reference arm
