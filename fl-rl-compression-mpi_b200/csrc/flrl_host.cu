@@ -66,6 +66,13 @@ struct Dev {
     uint8_t* bounce[2] = {nullptr, nullptr};
     uint64_t* h_scal = nullptr;  // pinned: small results read back from the device
     DBuf in, a, b, ws, scal, gather;  // device buffers (grow-only)
+    // chunk pipeline (one GPU, pinned host buffers): copy-in and copy-out streams beside the kernel stream `s`,
+    // two slots of device buffers, per-slot events
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t in_done[2] = {nullptr, nullptr}, k_start[2] = {nullptr, nullptr}, k_done[2] = {nullptr, nullptr},
+                out_done[2] = {nullptr, nullptr};
+    DBuf pin[2], pa[2], pb[2];
+    bool pipe_ready = false;
     float kernel_ms = 0, total_ms = 0;
 
     int init(int dev)
@@ -79,6 +86,20 @@ struct Dev {
         CK(cudaHostAlloc(&h_scal, 64 * sizeof(uint64_t), cudaHostAllocPortable));
         if (scal.ensure(64 * sizeof(uint64_t))) return -1;
         ready = true;
+        return 0;
+    }
+    int need_pipe()
+    {
+        if (pipe_ready) return 0;
+        CK(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            CK(cudaEventCreateWithFlags(&in_done[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&out_done[i], cudaEventDisableTiming));
+            CK(cudaEventCreate(&k_start[i]));
+            CK(cudaEventCreate(&k_done[i]));
+        }
+        pipe_ready = true;
         return 0;
     }
     int need_bounce()
@@ -158,6 +179,71 @@ struct DeviceGuard {
     DeviceGuard() { if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); dev = -1; } }
     ~DeviceGuard() { if (dev >= 0) cudaSetDevice(dev); }
 };
+
+
+// ---------------------------------------------------------------------------------------------
+// Chunk pipeline of the single-GPU host calls (file_io's "pinned, double-buffered cudaMemcpyAsync"): the input is cut
+// into chunks that encode / decode independently (FL: 128-byte aligned; RL: prev_run + 255 bytes of look-ahead, exactly
+// the shard rule of the multi-GPU path), and chunk i+1 is copied in while chunk i runs and chunk i-1 is copied out —
+// PCIe is full duplex, so a call costs max(bytes in, bytes out) instead of their sum.  Used when every host buffer
+// of the call is pinned (flrl_host_alloc); pageable buffers keep the bounce-buffer path.
+//   copy_in(i, slot)  enqueues the H2D copies of chunk i on d.s_in
+//   launch(i, slot)   enqueues the kernel (+ the read-back of its 8-byte result / status into d.h_scal) on d.s
+//   copy_out(i, slot) is called once the kernel of chunk i has finished (its result is in d.h_scal): enqueues the D2H
+//                     copies on d.s_out
+// chunk size: 64 MiB (about 1.1 ms of PCIe 5 x16 each way); FLRL_PIPE_CHUNK overrides it (tests use small chunks)
+size_t pipe_chunk_bytes()
+{
+    const char* e = getenv("FLRL_PIPE_CHUNK");
+    size_t c = e ? strtoull(e, nullptr, 10) : (size_t)(64u << 20);
+    c &= ~(size_t)4095;
+    return c < 65536 ? 65536 : c;
+}
+inline uint64_t* pipe_result(Dev& d, int slot) { return d.h_scal + 48 + 4 * slot; }              // pinned host
+inline uint64_t* pipe_result_dev(Dev& d, int slot) { return reinterpret_cast<uint64_t*>(d.scal.p) + 48 + 4 * slot; }
+
+template <class In, class Launch, class Out>
+int run_pipeline(Dev& d, size_t nchunks, In copy_in, Launch launch, Out copy_out)
+{
+    if (d.need_pipe()) return -1;
+    float kernel_ms = 0;
+    CK(cudaEventRecord(d.t0, d.s));
+    CK(cudaStreamWaitEvent(d.s_in, d.t0, 0));
+    auto finish = [&](size_t i) -> int {
+        const int slot = (int)(i & 1);
+        CK(cudaEventSynchronize(d.k_done[slot]));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, d.k_start[slot], d.k_done[slot]));
+        kernel_ms += ms;
+        if (int rc = copy_out(i, slot)) return rc;
+        CK(cudaEventRecord(d.out_done[slot], d.s_out));
+        return 0;
+    };
+    for (size_t i = 0; i < nchunks; ++i) {
+        const int slot = (int)(i & 1);
+        if (i >= 2) {
+            CK(cudaStreamWaitEvent(d.s_in, d.k_done[slot], 0));   // the kernel of chunk i-2 has read this slot's input
+            CK(cudaStreamWaitEvent(d.s, d.out_done[slot], 0));    // chunk i-2's output has left this slot's buffers
+        }
+        if (int rc = copy_in(i, slot)) return rc;
+        CK(cudaEventRecord(d.in_done[slot], d.s_in));
+        CK(cudaStreamWaitEvent(d.s, d.in_done[slot], 0));
+        CK(cudaEventRecord(d.k_start[slot], d.s));
+        if (int rc = launch(i, slot)) return rc;
+        CK(cudaEventRecord(d.k_done[slot], d.s));
+        CK(cudaStreamWaitEvent(d.s_out, d.k_done[slot], 0));
+        if (i >= 1)
+            if (int rc = finish(i - 1)) return rc;
+    }
+    if (int rc = finish(nchunks - 1)) return rc;
+    CK(cudaStreamWaitEvent(d.s, d.out_done[(nchunks - 1) & 1], 0));
+    if (nchunks >= 2) CK(cudaStreamWaitEvent(d.s, d.out_done[(nchunks - 2) & 1], 0));
+    CK(cudaEventRecord(d.t1, d.s));
+    CK(cudaStreamSynchronize(d.s));
+    CK(cudaEventElapsedTime(&d.total_ms, d.t0, d.t1));
+    d.kernel_ms = kernel_ms;
+    return 0;
+}
 
 // Number of GPUs the call uses and their ordinals: one GPU = the caller's CURRENT device (so a rank of a
 // multi-process job stays on its own GPU); several = devices 0 .. G-1.
@@ -344,6 +430,196 @@ int deliver(int G, uint8_t* dst, const std::vector<const uint8_t*>& src, const s
     });
 }
 
+
+// ------------------------------------------------------------------ the four calls on the chunk pipeline (one GPU)
+int fl_compress_pipelined(Dev& d, const uint8_t* data, size_t size, uint8_t* bits, uint8_t* values, size_t values_cap, size_t* values_size)
+{
+    const size_t PIPE_CHUNK = pipe_chunk_bytes();
+    const size_t nch = (size + PIPE_CHUNK - 1) / PIPE_CHUNK;
+    for (int k = 0; k < 2; ++k)
+        if (d.pin[k].ensure(PIPE_CHUNK) || d.pa[k].ensure(PIPE_CHUNK / 128) || d.pb[k].ensure(PIPE_CHUNK)) return -1;
+    if (d.ws.ensure(fl_workspace_bytes(PIPE_CHUNK))) return -1;
+    uint64_t voff = 0;
+    int rc = run_pipeline(
+        d, nch,
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, size - c0);
+            CK(cudaMemcpyAsync(d.pin[k].p, data + c0, n, cudaMemcpyHostToDevice, d.s_in));
+            return 0;
+        },
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, size - c0);
+            CK(fl_encode_launch(d.pin[k].p, n, d.pa[k].p, d.pb[k].p, pipe_result_dev(d, k), d.ws.p, d.s));
+            CK(cudaMemcpyAsync(pipe_result(d, k), pipe_result_dev(d, k), sizeof(uint64_t), cudaMemcpyDeviceToHost, d.s));
+            return 0;
+        },
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, size - c0);
+            const uint64_t vs = *pipe_result(d, k);
+            if (voff + vs > values_cap) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_compress: values capacity %zu too small", values_cap);
+            CK(cudaMemcpyAsync(bits + c0 / 128, d.pa[k].p, (n + 127) / 128, cudaMemcpyDeviceToHost, d.s_out));
+            if (vs) CK(cudaMemcpyAsync(values + voff, d.pb[k].p, vs, cudaMemcpyDeviceToHost, d.s_out));
+            voff += vs;
+            return 0;
+        });
+    *values_size = voff;
+    return rc;
+}
+
+int fl_decompress_pipelined(Dev& d, size_t output_size, const uint8_t* bits, const uint8_t* values, size_t values_size, uint8_t* out)
+{
+    const size_t PIPE_CHUNK = pipe_chunk_bytes();
+    const size_t nch = (output_size + PIPE_CHUNK - 1) / PIPE_CHUNK, frames = (output_size + 127) / 128;
+    for (int k = 0; k < 2; ++k)
+        if (d.pin[k].ensure(PIPE_CHUNK + 16) || d.pa[k].ensure(PIPE_CHUNK / 128 + 16) || d.pb[k].ensure(PIPE_CHUNK + 16)) return -1;
+    if (d.ws.ensure(fl_workspace_bytes(PIPE_CHUNK))) return -1;
+    // value bytes of every chunk: 16 * sum of its widths (the container's last frame may be partial)
+    std::vector<uint64_t> voff(nch + 1, 0);
+    for (size_t i = 0; i < nch; ++i) {
+        const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, output_size - c0);
+        uint64_t sum = 0;
+        for (size_t f = c0 / 128; f < c0 / 128 + n / 128; ++f) sum += bits[f];
+        uint64_t v = 16 * sum;
+        if (n % 128) v += ((n % 128) * bits[frames - 1] + 7) / 8;
+        voff[i + 1] = voff[i] + v;
+    }
+    if (voff[nch] > values_size) return fail(FLRL_E_FORMAT, "flrl_fl_gpu_decompress: values shorter than the widths imply");
+    bool bad = false;
+    int rc = run_pipeline(
+        d, nch,
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, output_size - c0);
+            CK(cudaMemcpyAsync(d.pa[k].p, bits + c0 / 128, (n + 127) / 128, cudaMemcpyHostToDevice, d.s_in));
+            if (voff[i + 1] > voff[i]) CK(cudaMemcpyAsync(d.pin[k].p, values + voff[i], voff[i + 1] - voff[i], cudaMemcpyHostToDevice, d.s_in));
+            return 0;
+        },
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, output_size - c0);
+            CK(fl_decode_launch(d.pa[k].p, (n + 127) / 128, d.pin[k].p, voff[i + 1] - voff[i], d.pb[k].p, n, d.ws.p, d.s));
+            CK(cudaMemcpyAsync(pipe_result(d, k), fl_decode_status(d.ws.p, n), sizeof(int), cudaMemcpyDeviceToHost, d.s));
+            return 0;
+        },
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, output_size - c0);
+            if (*reinterpret_cast<int*>(pipe_result(d, k))) bad = true;
+            CK(cudaMemcpyAsync(out + c0, d.pb[k].p, n, cudaMemcpyDeviceToHost, d.s_out));
+            return 0;
+        });
+    if (rc) return rc;
+    if (bad) return fail(FLRL_E_FORMAT, "flrl_fl_gpu_decompress: malformed container (GPU 0)");
+    return 0;
+}
+
+int rl_compress_pipelined(Dev& d, const uint8_t* data, size_t size, uint8_t* counts, uint8_t* values, size_t pair_cap, size_t* pairs)
+{
+    const size_t PIPE_CHUNK = pipe_chunk_bytes();
+    const size_t nch = (size + PIPE_CHUNK - 1) / PIPE_CHUNK;
+    for (int k = 0; k < 2; ++k)
+        if (d.pin[k].ensure(PIPE_CHUNK + 256 + 16) || d.pa[k].ensure(PIPE_CHUNK) || d.pb[k].ensure(PIPE_CHUNK)) return -1;
+    if (d.ws.ensure(rl_encode_workspace_bytes(PIPE_CHUNK))) return -1;
+    // the run every chunk continues: bytes equal to its first byte immediately before it (carried over whole chunks)
+    std::vector<uint64_t> prev(nch, 0);
+    for (size_t i = 1; i < nch; ++i) {
+        const size_t c0 = i * PIPE_CHUNK;
+        uint64_t r = 0;
+        while (r < PIPE_CHUNK && data[c0 - 1 - r] == data[c0]) ++r;
+        if (r == PIPE_CHUNK && data[c0 - PIPE_CHUNK] == data[c0]) r += prev[i - 1];  // the whole previous chunk is part of the run
+        prev[i] = r;
+    }
+    uint64_t off = 0;
+    int rc = run_pipeline(
+        d, nch,
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, size - c0), ahead = std::min<size_t>(255, size - (c0 + n));
+            CK(cudaMemcpyAsync(d.pin[k].p, data + c0, n + ahead, cudaMemcpyHostToDevice, d.s_in));
+            return 0;
+        },
+        [&](size_t i, int k) -> int {
+            const size_t c0 = i * PIPE_CHUNK, n = std::min(PIPE_CHUNK, size - c0), ahead = std::min<size_t>(255, size - (c0 + n));
+            CK(rl_encode_launch(d.pin[k].p, n, n + ahead, prev[i], d.pa[k].p, d.pb[k].p, PIPE_CHUNK, pipe_result_dev(d, k), d.ws.p, d.s));
+            CK(cudaMemcpyAsync(pipe_result(d, k), pipe_result_dev(d, k), sizeof(uint64_t), cudaMemcpyDeviceToHost, d.s));
+            return 0;
+        },
+        [&](size_t, int k) -> int {
+            const uint64_t np = *pipe_result(d, k);
+            if (off + np > pair_cap) return fail(FLRL_E_CAPACITY, "flrl_rl_gpu_compress: pair capacity %zu too small", pair_cap);
+            if (np) {
+                CK(cudaMemcpyAsync(counts + off, d.pa[k].p, np, cudaMemcpyDeviceToHost, d.s_out));
+                CK(cudaMemcpyAsync(values + off, d.pb[k].p, np, cudaMemcpyDeviceToHost, d.s_out));
+            }
+            off += np;
+            return 0;
+        });
+    *pairs = off;
+    return rc;
+}
+
+int rl_decompress_pipelined(Dev& d, const uint8_t* counts, const uint8_t* values, size_t pairs, uint8_t* out, size_t out_cap, size_t* out_size)
+{
+    const size_t PIPE_CHUNK = pipe_chunk_bytes();
+    // pairs per chunk: about PIPE_CHUNK bytes of pairs + output per chunk at the stream's mean count (out_cap is the
+    // decoded size the caller expects); a chunk's output buffer holds the worst case, 255 bytes per pair
+    const size_t mean = std::max<size_t>(1, out_cap / pairs);
+    const size_t PIPE_PAIRS = std::min<size_t>(16u << 20, std::max<size_t>(64u << 10, (PIPE_CHUNK / (2 + mean)) & ~(size_t)4095));
+    const size_t nch = (pairs + PIPE_PAIRS - 1) / PIPE_PAIRS;
+    const size_t ocap = std::min<size_t>(255 * PIPE_PAIRS, out_cap) + 16;
+    for (int k = 0; k < 2; ++k)
+        if (d.pa[k].ensure(PIPE_PAIRS + 16) || d.pb[k].ensure(PIPE_PAIRS + 16) || d.pin[k].ensure(ocap)) return -1;
+    if (d.ws.ensure(rl_decode_workspace_bytes(PIPE_PAIRS))) return -1;
+    uint64_t off = 0;
+    bool bad = false, over = false;
+    int rc = run_pipeline(
+        d, nch,
+        [&](size_t i, int k) -> int {
+            const size_t p0 = i * PIPE_PAIRS, np = std::min(PIPE_PAIRS, pairs - p0);
+            CK(cudaMemcpyAsync(d.pa[k].p, counts + p0, np, cudaMemcpyHostToDevice, d.s_in));
+            CK(cudaMemcpyAsync(d.pb[k].p, values + p0, np, cudaMemcpyHostToDevice, d.s_in));
+            return 0;
+        },
+        [&](size_t i, int k) -> int {
+            const size_t p0 = i * PIPE_PAIRS, np = std::min(PIPE_PAIRS, pairs - p0);
+            CK(rl_decode_launch(d.pa[k].p, d.pb[k].p, np, d.pin[k].p, ocap - 16, pipe_result_dev(d, k), d.ws.p, d.s));
+            CK(cudaMemcpyAsync(pipe_result(d, k), pipe_result_dev(d, k), sizeof(uint64_t), cudaMemcpyDeviceToHost, d.s));
+            CK(cudaMemcpyAsync(pipe_result(d, k) + 1, rl_decode_status(d.ws.p, np), sizeof(int), cudaMemcpyDeviceToHost, d.s));
+            return 0;
+        },
+        [&](size_t, int k) -> int {
+            const uint64_t nb = *pipe_result(d, k);
+            const int st = *reinterpret_cast<int*>(pipe_result(d, k) + 1);
+            if (st == 2) bad = true;
+            if (st == 1 || off + nb > out_cap) over = true;
+            if (!bad && !over && nb) CK(cudaMemcpyAsync(out + off, d.pin[k].p, nb, cudaMemcpyDeviceToHost, d.s_out));
+            off += nb;
+            return 0;
+        });
+    if (rc) return rc;
+    if (bad) return fail(FLRL_E_FORMAT, "flrl_rl_gpu_decompress: malformed pair stream (GPU 0)");
+    if (over) return fail(FLRL_E_CAPACITY, "flrl_rl_gpu_decompress: decoded size %llu exceeds the output capacity %zu", (unsigned long long)off, out_cap);
+    *out_size = off;
+    return 0;
+}
+
+// the pipeline applies to one GPU, inputs of more than one chunk, and pinned host buffers
+bool pipe_ok(int G, size_t bytes, std::initializer_list<const void*> bufs)
+{
+    static const bool off = getenv("FLRL_NO_PIPELINE") != nullptr;
+    if (off || G != 1 || bytes <= pipe_chunk_bytes()) return false;
+    for (const void* b : bufs)
+        if (!is_pinned(b)) return false;
+    return true;
+}
+
+// runs `op` on the call's single GPU (set up like the sharded path does) and publishes its timing
+template <class Op>
+int on_single_gpu(Op op)
+{
+    Dev& d = g_dev[g_map[0]];
+    CK(cudaSetDevice(g_map[0]));
+    if (d.init(g_map[0])) return -1;
+    if (int rc = op(d)) return rc;
+    collect_timing(1);
+    return 0;
+}
 }  // namespace
 
 extern "C" {
@@ -384,6 +660,12 @@ int flrl_fl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
     if (size < (size_t)G * 16384 && G > 1) { G = 1; single_gpu_map(); }
     const size_t frames = (size + FRAME_LENGTH_ - 1) / FRAME_LENGTH_;
     if (bits_cap < frames) return fail(FLRL_E_CAPACITY, "flrl_fl_gpu_compress: bits capacity %zu < %zu", bits_cap, frames);
+    if (pipe_ok(G, size, {data, bits, values})) {
+        int rc = on_single_gpu([&](Dev& d) { return fl_compress_pipelined(d, data, size, bits, values, values_cap, values_size); });
+        if (rc) { *values_size = 0; return rc; }
+        *bits_size = frames;
+        return FLRL_OK;
+    }
 
     int rc = for_each_gpu(G, [&](int g) -> int {
         Dev& d = g_dev[g_map[g]];
@@ -479,6 +761,12 @@ int flrl_fl_gpu_decompress_into(size_t output_size, const uint8_t* bits, size_t 
     int G = 1;
     if (int rc = device_count(ngpus, &G)) return rc;
     if (output_size < (size_t)G * 16384 && G > 1) { G = 1; single_gpu_map(); }
+    if (pipe_ok(G, output_size, {bits, values, out})) {
+        int rc = on_single_gpu([&](Dev& d) { return fl_decompress_pipelined(d, output_size, bits, values, values_size, out); });
+        if (rc) return rc;
+        *out_size = output_size;
+        return FLRL_OK;
+    }
 
     // phase A: widths of each shard to its GPU, sum of widths -> value bytes of the shard
     int rc = for_each_gpu(G, [&](int g) -> int {
@@ -561,6 +849,11 @@ int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
     int G = 1;
     if (int rc = device_count(ngpus, &G)) return rc;
     if (size < (size_t)G * 16384 && G > 1) { G = 1; single_gpu_map(); }
+    if (pipe_ok(G, size, {data, counts, values})) {
+        int rc = on_single_gpu([&](Dev& d) { return rl_compress_pipelined(d, data, size, counts, values, pair_cap, pairs); });
+        if (rc) *pairs = 0;
+        return rc ? rc : FLRL_OK;
+    }
     int rc = for_each_gpu(G, [&](int g) -> int {
         Dev& d = g_dev[g_map[g]];
         CK(cudaSetDevice(g_map[g]));
@@ -643,6 +936,11 @@ int flrl_rl_gpu_decompress_into(const uint8_t* counts, const uint8_t* values, si
     int G = 1;
     if (int rc = device_count(ngpus, &G)) return rc;
     if (pairs < (size_t)G * 4096 && G > 1) { G = 1; single_gpu_map(); }
+    if (pipe_ok(G, 2 * pairs + out_cap, {counts, values, out})) {
+        int rc = on_single_gpu([&](Dev& d) { return rl_decompress_pipelined(d, counts, values, pairs, out, out_cap, out_size); });
+        if (rc) *out_size = 0;
+        return rc ? rc : FLRL_OK;
+    }
     // phase A: pairs of each shard to its GPU, sum of counts -> output bytes of the shard
     int rc = for_each_gpu(G, [&](int g) -> int {
         Dev& d = g_dev[g_map[g]];

@@ -61,6 +61,26 @@ def test_host_pinned_round_trip(kind, oracle, flrl):
         assert 0 < k_ms <= t_ms
 
 
+@pytest.mark.parametrize("kind,mean", [("fl", 0), ("rl", 40), ("rl", 3), ("rl", 3_000_000)])
+def test_host_chunk_pipeline(kind, mean, oracle, flrl, monkeypatch):
+    """The single-GPU chunk pipeline (copy-in / kernel / copy-out overlapped, pinned buffers) with small chunks: chunk
+    outputs must concatenate to the single-stream output (FL: 128-aligned chunks; RL: prev_run + look-ahead, runs
+    longer than a chunk carried over whole chunks)."""
+    monkeypatch.setenv("FLRL_PIPE_CHUNK", str(1 << 20))
+    n = (11 << 20) + 128 * 5 + 77
+    data = make_fl_mix(n, seed=5) if kind == "fl" else _rl_data(n, mean, 6)
+    hc = flrl.HostCodec(kind, n, ngpus=1)
+    hc.load_input(data)
+    hc.compress()
+    meta, payload = hc.compressed()
+    m_ref, p_ref = (oracle.fl_compress if kind == "fl" else oracle.rl_compress)(data)
+    assert np.array_equal(meta, m_ref) and np.array_equal(payload, p_ref), kind
+    hc.decompress()
+    assert hc.check_round_trip(), kind
+    k_ms, t_ms = hc.timing()
+    assert 0 < k_ms <= t_ms
+
+
 @pytest.mark.parametrize("peer", [0, 1])
 def test_multi_gpu_concat_identity(peer, oracle, flrl):
     """Shards + NCCL size all-gather + concatenation == single-stream output, both concat modes."""
