@@ -27,8 +27,8 @@ __device__ __forceinline__ void st_relaxed_u64x2(uint64_t* p, uint64_t x, uint64
 __device__ __forceinline__ bool all_posted(const uint4& v) { return ((v.x & v.y & v.z & v.w) >> 31) != 0; }
 __device__ __forceinline__ void scan_pair_counts(const uint32_t* __restrict__ agg, uint64_t* __restrict__ inc, long long tiles, int lane)
 {
-    // the arrays are padded to a multiple of 256 entries (rl_encode_tiles), so whole chunks can be read and written;
-    // entries at or past `tiles` are never posted and count as 0
+    // the arrays are padded to a multiple of 256 entries, so whole chunks can be read and written; entries at or past
+    // `tiles` are never posted and count as 0
     uint64_t base = 0;
     const long long chunks = (tiles + 255) / 256;
     ScanRegs cur, nxt;
@@ -40,45 +40,57 @@ __device__ __forceinline__ void scan_pair_counts(const uint32_t* __restrict__ ag
             nxt.a = ld_relaxed_u32x4(agg + t0 + 256);
             nxt.b = ld_relaxed_u32x4(agg + t0 + 260);
         }
-        const bool real_a = t0 + 4 <= tiles, real_b = t0 + 8 <= tiles;  // groups that hold only real tiles
+        // An answer must never wait for a LATER tile (the CTA that holds that tile may itself be waiting for this
+        // answer): `front` = entries of the chunk already answered; every round answers all entries up to the first
+        // one that is still empty.  Normally the whole chunk is there at the first look (one round, vector stores).
+        uint32_t front = 0;
         while (true) {
-            // a group that reaches past the last tile is checked entry by entry
-            bool ok = true;
-            if (real_a) ok = all_posted(cur.a);
-            else {
-                if (t0 + 0 < tiles) ok = ok && (cur.a.x >> 31);
-                if (t0 + 1 < tiles) ok = ok && (cur.a.y >> 31);
-                if (t0 + 2 < tiles) ok = ok && (cur.a.z >> 31);
+            uint32_t v[8] = {cur.a.x, cur.a.y, cur.a.z, cur.a.w, cur.b.x, cur.b.y, cur.b.z, cur.b.w};
+            uint32_t lv = 0;  // leading entries of this lane that are posted (entries past the last tile count as posted)
+            bool open = true;
+            uint32_t ex[8], run = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const bool real = t0 + j < tiles;
+                open = open && (!real || (v[j] >> 31));
+                lv += open ? 1u : 0u;
+                ex[j] = run;
+                run += (open && real) ? (v[j] & 0x7fffffffu) : 0u;
             }
-            bool okb = true;
-            if (real_b) okb = all_posted(cur.b);
-            else {
-                if (t0 + 4 < tiles) okb = okb && (cur.b.x >> 31);
-                if (t0 + 5 < tiles) okb = okb && (cur.b.y >> 31);
-                if (t0 + 6 < tiles) okb = okb && (cur.b.z >> 31);
+            const unsigned fullm = __ballot_sync(0xffffffffu, lv == 8);
+            const uint32_t r = fullm == 0xffffffffu ? 32u : (uint32_t)__ffs(~fullm) - 1u;  // leading lanes that are complete
+            const uint32_t lv_r = __shfl_sync(0xffffffffu, lv, r & 31u);
+            const uint32_t new_front = r == 32u ? 256u : 8u * r + lv_r;
+            // exclusive prefix over lanes 0 .. r (lane r with its leading posted entries only)
+            uint32_t s = (uint32_t)lane <= r ? run : 0u;
+            const uint32_t mine = s;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, s, d);
+                if (lane >= d) s += o;
             }
-            if (!__any_sync(0xffffffffu, !(ok && okb))) break;
-            if (!ok) cur.a = ld_relaxed_u32x4(agg + t0);
-            if (!okb) cur.b = ld_relaxed_u32x4(agg + t0 + 4);
-        }
-        uint32_t v[8] = {cur.a.x, cur.a.y, cur.a.z, cur.a.w, cur.b.x, cur.b.y, cur.b.z, cur.b.w};
-        uint32_t ex[8], run = 0;
+            const uint64_t lb = base + (s - mine);
+            if (front == 0 && new_front == 256u) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            ex[j] = run;
-            run += (t0 + j < tiles) ? (v[j] & 0x7fffffffu) : 0u;
-        }
-        uint32_t s = run;
+                for (int j = 0; j < 8; j += 2)
+                    st_relaxed_u64x2(inc + t0 + j, (1ull << 63) | (lb + ex[j]), (1ull << 63) | (lb + ex[j + 1]));
+            } else {
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t o = __shfl_up_sync(0xffffffffu, s, d);
-            if (lane >= d) s += o;
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t pos = 8u * lane + j;
+                    if (pos >= front && pos < new_front) st_relaxed_u64(inc + t0 + j, (1ull << 63) | (lb + ex[j]));
+                }
+            }
+            front = new_front;
+            if (front == 256u) {
+                base += __shfl_sync(0xffffffffu, s, 31);
+                break;
+            }
+            if (lv < 8) {  // poll the groups that still hold an empty entry
+                if (lv < 4) cur.a = ld_relaxed_u32x4(agg + t0);
+                cur.b = ld_relaxed_u32x4(agg + t0 + 4);
+            }
         }
-        const uint64_t lb = base + (s - run);
-#pragma unroll
-        for (int j = 0; j < 8; j += 2)
-            st_relaxed_u64x2(inc + t0 + j, (1ull << 63) | (lb + ex[j]), (1ull << 63) | (lb + ex[j + 1]));
-        base += __shfl_sync(0xffffffffu, s, 31);
         cur = nxt;
     }
 }
