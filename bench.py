@@ -242,6 +242,7 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     flrl = importlib.import_module("fl-rl-compression-mpi_b200")  # raises if libflrl.so is missing: no fallback
+    sharding = importlib.import_module("fl-rl-compression-mpi_b200.sharding")
     n = args.bytes
     work = make_work(flrl, torch, args.workload, n, rank)
 
@@ -255,27 +256,14 @@ def run_ours(args):
     def exchange():
         """N > 1, inside every timed step: the ONLY exchange of the path — all-gather the per-shard compressed sizes
         (one u64 per GPU, NCCL) and turn them into output offsets by an exclusive scan, on the device, no host sync."""
-        dist.all_gather_into_tensor(sizes, work.size_tensor())
-        torch.cumsum(sizes, 0, out=offsets)
-        offsets.sub_(sizes)
+        sharding.exchange_sizes(dist, work.size_tensor(), sizes, offsets)  # the logic tests/test_sharding_gloo.py runs over gloo
 
     def concat_to_rank0():
         """The device-resident merge of the reference's gpuNCCLCompress (fl_gpu.cu:221-238): every rank sends its payload
         to its offset in rank 0's buffer (NCCL send/recv over NVLink).  It serialises on rank 0's ingress link, so it
         is measured on its own (detail.concat_to_rank0_ms) and is not part of the timed step: end to end, every GPU
         delivers its payload straight to its offset in the host buffer instead (host layer, e2e)."""
-        s = sizes.tolist()
-        offs = [0]
-        for x in s:
-            offs.append(offs[-1] + x)
-        if rank == 0:
-            gather_buf[: s[0]].copy_(work.payload()[: s[0]], non_blocking=True)
-            ops = [dist.P2POp(dist.irecv, gather_buf[offs[r]:offs[r + 1]], r) for r in range(1, world) if s[r]]
-        else:
-            ops = [dist.P2POp(dist.isend, work.payload()[: s[rank]], 0)] if s[rank] else []
-        if ops:
-            for req in dist.batch_isend_irecv(ops):
-                req.wait()
+        sharding.concat_to_rank0(dist, work.payload(), sizes, rank, gather_buf)
 
     def step():
         work.encode()
