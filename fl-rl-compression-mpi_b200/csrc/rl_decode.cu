@@ -10,10 +10,10 @@
 //     output byte.  By the time the compute warps reach the tile, that answer is normally there: no tile
 //     waits for a look-back;
 //   * 8 compute warps: block scan of the counts -> exclusive starts in shared memory (":164-171") + a table
-//     "pair that covers output byte b << sh" -> every thread owns 16-byte chunks aligned in the
-//     OUTPUT address space, finds the covering pair by a binary search (":172-179") that the table narrows to the
-//     pairs of one block (0-1 steps instead of 12), and XORs value deltas into two
-//     64-bit words -> coalesced 128-bit stores.
+//     "pair that covers output byte b << sh" -> every thread owns 64-byte units aligned in the OUTPUT
+//     address space, finds the pair covering the unit's first byte by a binary search (":172-179") that the table narrows to the
+//     pairs of one block (0-1 steps instead of 12), walks the pairs of the unit and XORs value deltas
+//     into 64-bit words -> 256-bit stores (STG.256: whole 32-byte sectors).
 #include <stdlib.h>
 
 #include <algorithm>
@@ -215,16 +215,16 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
         }
         bar_sync(BAR_D, RLD_THREADS);  // B: offs, tbl
 
-        // ---- expand: 16-byte chunks aligned in the OUTPUT address space
+        // ---- expand: every thread owns 64-byte units (two 32-byte stores, 32-byte aligned in the OUTPUT address space):
+        // one search per unit, then a walk over the pairs of its four 16-byte pieces
         const uint64_t O = obase_s[k & 1u];
         const uint64_t lim = out_cap > O ? (out_cap - O < total ? out_cap - O : total) : 0;  // bytes of this tile that fit
         const uint32_t tot = (uint32_t)lim;
-        const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(out) + O) & 15u);
-        const uint32_t nchunks = tot ? (mis + tot + 15u) >> 4 : 0u;
-        for (uint32_t q = tid; q < nchunks; q += RLD_THREADS) {
-            const int p = (int)(16u * q) - (int)mis;  // tile-relative output position of the chunk's first byte
+        const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(out) + O) & 31u);
+        const uint32_t nunits = tot ? (mis + tot + 63u) >> 6 : 0u;
+        for (uint32_t q = tid; q < nunits; q += RLD_THREADS) {
+            const int p = (int)(64u * q) - (int)mis;  // tile-relative output position of the unit's first byte
             const uint32_t lo = p < 0 ? 0u : (uint32_t)p;
-            const uint32_t hi = (uint32_t)(p + 16) < tot ? (uint32_t)(p + 16) : tot;
             // j = last pair with offs[j] <= lo  (IMPLEMENTATION-PLAN.md:164-179, binary search)
             uint32_t a = 0, b = np;  // invariant: offs[a] <= lo, offs[b] > lo (offs[np] = total > lo)
             {
@@ -239,30 +239,41 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
             uint32_t j = a;
             uint32_t pv = val[j];
             uint32_t end = offs[j + 1];
-            uint64_t x_lo, x_hi;
-            {
-                const uint32_t v4 = pv * 0x01010101u;
-                x_lo = ((uint64_t)v4 << 32) | v4;
-                x_hi = x_lo;
-            }
-            while (end < hi) {
-                ++j;
-                const uint32_t nv = val[j];
-                const uint32_t d4 = (nv ^ pv) * 0x01010101u;
-                const uint64_t d8 = ((uint64_t)d4 << 32) | d4;
-                const uint32_t at = end - (uint32_t)p;  // 1..15: first byte of the chunk owned by pair j
-                x_lo ^= shl64c(d8, 8 * at);
-                x_hi ^= at < 8 ? d8 : shl64c(d8, 8 * at - 64);
-                pv = nv;
-                end = offs[j + 1];
-            }
             uint8_t* dst = out + O + p;
-            if (p >= 0 && (uint32_t)p + 16u <= tot) {
-                *reinterpret_cast<uint4*>(dst) = make_uint4((uint32_t)x_lo, (uint32_t)(x_lo >> 32), (uint32_t)x_hi, (uint32_t)(x_hi >> 32));
-            } else {
-                for (uint32_t kk = lo; kk < hi; ++kk) {
-                    const uint32_t bi = kk - (uint32_t)p;
-                    dst[bi] = (uint8_t)((bi < 8 ? x_lo >> (8 * bi) : x_hi >> (8 * bi - 64)) & 0xff);
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                uint64_t w[4];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int ph = p + 32 * half + 16 * h;  // first byte of the 16-byte piece
+                    const uint32_t hi = ph + 16 <= 0 ? 0u : ((uint32_t)(ph + 16) < tot ? (uint32_t)(ph + 16) : tot);
+                    const uint32_t v4 = pv * 0x01010101u;
+                    uint64_t x_lo = ((uint64_t)v4 << 32) | v4, x_hi = x_lo;
+                    while (end < hi) {
+                        ++j;
+                        const uint32_t nv = val[j];
+                        const uint32_t d4 = (nv ^ pv) * 0x01010101u;
+                        const uint64_t d8 = ((uint64_t)d4 << 32) | d4;
+                        const uint32_t at = end - (uint32_t)ph;  // 0..15: first byte of the piece owned by pair j
+                        x_lo ^= shl64c(d8, 8 * at);
+                        x_hi ^= at < 8 ? d8 : shl64c(d8, 8 * at - 64);
+                        pv = nv;
+                        end = offs[j + 1];
+                    }
+                    w[2 * h] = x_lo;
+                    w[2 * h + 1] = x_hi;
+                }
+                const int ps = p + 32 * half;
+                if (ps >= 0 && (uint32_t)ps + 32u <= tot) {
+                    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 32 * half), "r"((uint32_t)w[0]),
+                                 "r"((uint32_t)(w[0] >> 32)), "r"((uint32_t)w[1]), "r"((uint32_t)(w[1] >> 32)), "r"((uint32_t)w[2]),
+                                 "r"((uint32_t)(w[2] >> 32)), "r"((uint32_t)w[3]), "r"((uint32_t)(w[3] >> 32))
+                                 : "memory");
+                } else {
+                    for (int bi = 0; bi < 32; ++bi) {
+                        const int pos = ps + bi;
+                        if (pos >= 0 && (uint32_t)pos < tot) dst[32 * half + bi] = (uint8_t)(w[bi >> 3] >> (8 * (bi & 7)));
+                    }
                 }
             }
         }
