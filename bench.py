@@ -386,12 +386,12 @@ def run_ours(args):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) from the committed `ncu --set full` captures
-# (profiles/r01_run5_*_ncu_full.csv; 1 GiB per launch, the bench's default size)
+# (profiles/r01_run6_*_ncu_full.csv; 1 GiB per launch, the bench's default size)
 TRAFFIC = {
     ("fl", "fl_encode_kernel"): 1_640_366_000, ("fl", "fl_decode_kernel"): 1_641_514_000,
-    ("rl4", "rl_encode_kernel"): 1_579_041_000, ("rl4", "rl_decode_kernel"): 1_553_995_000,
-    ("rl64", "rl_encode_kernel"): 1_110_635_000, ("rl64", "rl_decode_kernel"): 1_049_531_000,
-    ("rl4096", "rl_encode_kernel"): 1_088_694_000, ("rl4096", "rl_decode_kernel"): 1_024_660_000,
+    ("rl4", "rl_encode_kernel"): 1_579_041_000, ("rl4", "rl_decode_kernel"): 1_558_577_000,
+    ("rl64", "rl_encode_kernel"): 1_110_635_000, ("rl64", "rl_decode_kernel"): 1_057_315_000,
+    ("rl4096", "rl_encode_kernel"): 1_088_694_000, ("rl4096", "rl_decode_kernel"): 1_030_955_000,
 }
 
 
