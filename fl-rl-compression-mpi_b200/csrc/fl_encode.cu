@@ -1,0 +1,361 @@
+// fl_encode.cu — fixed-length encoder for sm_100a: one launch, input read from DRAM once, output written once.
+//
+// Replaces the reference's compress kernels + thrust scan + byte-atomic CAS loops
+// (/root/reference/src/fl/fl_gpu.cu:648-726, :758-808).
+//
+// The value offset of a tile needs the widths of every earlier tile.  Two touches per 128-frame tile (16 KiB),
+// FLE_LEAD iterations apart, by PERSISTENT CTAs (CTA c owns tiles c, c + G, c + 2G, ...; 4 pack warps + 1 service warp):
+//   * width touch of tile t (first touch: DRAM -> L2 -> shared memory, L2 evict-last): per-frame width from the OR
+//     of the frame (fl_cpu.cu:37-50) — one thread per frame, its eight 16-byte pieces read in a rotated order so
+//     that a quarter-warp covers all banks, no shuffles.  Warp 0 writes the 128 widths to `bits`, scans them once,
+//     keeps (offset, width) of every frame in a small shared-memory ring for the pack touch, and posts the tile's
+//     packed size (16-byte units: a full frame of width b packs to exactly 16 b bytes) to the grid's scanner warp
+//     (rl_scan.cuh), which turns sizes into offsets in tile order;
+//   * pack touch of tile t - FLE_LEAD * G, in the same loop iteration (second touch: an L2 hit, evict-first):
+//     (offset, width) from the ring, the tile's offset in `values` (posted thousands of tiles ago: one load, asked
+//     for at the top of the iteration), lane-local multiply/shift packing (flrl_bits.cuh; fl_cpu.cu:64-84; four
+//     lanes per frame) into an output slot, one TMA bulk store (every tile starts on a 16-byte boundary of `values`).
+// FLE_LEAD * G tiles (~45 MiB) exceed everything in flight and stay inside the 126 MB L2, so no CTA ever waits for
+// another one.  The service warp refills a slot as soon as its last reader is done; two named barriers per iteration.
+// The kernel is bound by instruction issue and latency in the pack warps (about 1000 instructions per warp and tile,
+// ~450 of them the packing), not by memory: without the packing arithmetic it runs at 86 % of the HBM bandwidth.
+// (History: one CTA per tile with a look-back, 0.417 ms / GiB; this structure with widths by shuffles and recomputed
+// in the pack touch, 0.42 ms; widths by one thread per frame + the (offset, width) ring, 0.36 ms.)
+//
+// The grid must be fully co-resident (tiles are assigned statically): the launcher sizes it from the occupancy API.
+//
+// Only the final partial frame (n % 128 != 0) goes through a small cooperative scalar path in the CTA that
+// owns the last tile, which also publishes the total value size.
+#include <stdlib.h>
+
+#include <algorithm>
+
+#include "fl_kernels.cuh"
+#include "flrl_bits.cuh"
+#include "rl_scan.cuh"
+
+namespace flrl {
+
+static constexpr int FLE_TILE_FRAMES = 128;
+static constexpr int FLE_TILE_BYTES = FLE_TILE_FRAMES * 128;  // 16 KiB
+#ifndef FLE_PACK
+#define FLE_PACK 128  // pack threads; four of them share a frame
+#endif
+static constexpr int FLE_THREADS = FLE_PACK + 32;             // + service warp
+static constexpr int FLE_ITEMS = 4 * FLE_TILE_FRAMES / FLE_PACK;  // 32-byte items per thread per tile
+// 16 KiB slots per CTA: width touch, pack touch, packed output.  One of each and 4 CTAs / SM measured best
+// (more slots with 3 CTAs / SM: 0.44 ms; 256 pack threads: 0.46 ms).
+#ifndef FLE_WSLOTS
+#define FLE_WSLOTS 1
+#endif
+#ifndef FLE_PSLOTS
+#define FLE_PSLOTS 1
+#endif
+#ifndef FLE_OSLOTS
+#define FLE_OSLOTS 1
+#endif
+#ifndef FLE_CTAS
+#define FLE_CTAS 4  // per SM
+#endif
+#ifndef FLE_LEAD
+#define FLE_LEAD 5  // iterations between the two touches of a tile
+#endif
+#ifndef FLE_EXP
+#define FLE_EXP 0  // timing experiments only (wrong output): 1 = no packing arithmetic, 2 = no width arithmetic
+#endif
+static constexpr uint32_t BAR_P = 1;  // named barrier of the pack warps
+
+struct FleShared {
+    uint8_t bw[2][FLE_TILE_FRAMES];  // width touch: widths (two copies: warp 0 reads one while the others fill the next)
+    // kept from the width touch to the pack touch FLE_LEAD iterations later: per frame (offset in 16-byte units) << 8 | width
+    __align__(16) uint32_t meta[FLE_LEAD + 1][FLE_TILE_FRAMES];
+    uint32_t total[FLE_LEAD + 1];    // packed size of the tile (16-byte units)
+};
+
+__device__ __forceinline__ uint32_t fle_byte_sum(uint32_t v) { return __dp4a(v, 0x01010101u, 0u); }
+
+// final partial frame (len = n % 128 in 1..127), the 128 pack threads participate
+// fl_cpu.cu:37-50 (width), :64-84 (packing), :53 (size = ceil(bits/8)).
+__device__ __noinline__ uint32_t fle_tail_frame(const uint8_t* in, uint32_t len, uint8_t* bits_out, uint8_t* vout,
+                                                uint32_t* scratch /* >= 35 words smem */)
+{
+    const int tid = threadIdx.x;
+    const uint32_t v = (tid < (int)len) ? in[tid] : 0u;
+    if (tid < 35) scratch[tid] = 0;
+    bar_sync(BAR_P, FLE_PACK);
+    const uint32_t wo = __reduce_or_sync(0xffffffffu, v);
+    if ((tid & 31) == 0 && wo) atomicOr(&scratch[34], wo);
+    bar_sync(BAR_P, FLE_PACK);
+    const uint32_t b = width_of_or(scratch[34]);
+    if (tid < (int)len) {
+        const uint32_t bit = tid * b;
+        const uint32_t w = bit >> 5, sh = bit & 31;
+        atomicOr(&scratch[w], v << sh);
+        if (sh + b > 32) atomicOr(&scratch[w + 1], v >> (32 - sh));
+    }
+    bar_sync(BAR_P, FLE_PACK);
+    const uint32_t nbytes = (len * b + 7) >> 3;
+    if (tid < (int)nbytes) vout[tid] = (uint8_t)(scratch[tid >> 2] >> (8 * (tid & 3)));
+    if (tid == 0) *bits_out = (uint8_t)b;
+    return nbytes;
+}
+
+__device__ __forceinline__ int fle_full_frames_of(size_t full_frames, long long tile)
+{
+    const size_t f0 = (size_t)tile * FLE_TILE_FRAMES;
+    return (int)(full_frames > f0 ? (full_frames - f0 < (size_t)FLE_TILE_FRAMES ? full_frames - f0 : FLE_TILE_FRAMES) : 0);
+}
+
+__global__ void __launch_bounds__(FLE_THREADS, FLE_CTAS)
+fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__ bits, uint8_t* __restrict__ values,
+                 uint64_t* __restrict__ values_size, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg, long long tiles)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t* const wbuf = smem;                                 // FLE_WSLOTS x 16 KiB: width touch
+    uint8_t* const pbuf = smem + FLE_WSLOTS * FLE_TILE_BYTES;   // FLE_PSLOTS x 16 KiB: pack touch
+    uint8_t* const obuf = pbuf + FLE_PSLOTS * FLE_TILE_BYTES;   // FLE_OSLOTS x 16 KiB: the packed tile, source of the bulk store
+    __shared__ __align__(8) uint64_t w_full[FLE_WSLOTS], w_free[FLE_WSLOTS], p_full[FLE_PSLOTS], p_free[FLE_PSLOTS];
+    __shared__ FleShared sh;
+    __shared__ __align__(16) uint4 ktab[9];  // PackK{k1,k2,k3,ra} per width
+    __shared__ uint32_t tail_scratch[36];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x == 0) {  // the scanner CTA
+        if (warp == 0) scan_pair_counts(agg, inc, tiles, lane);
+        return;
+    }
+    const long long G = gridDim.x - 1, c = blockIdx.x - 1;
+    const long long Kw = (tiles - c + G - 1) / G;  // tiles of this CTA: c, c + G, ...
+    const long long iters = Kw + FLE_LEAD;
+    const size_t full_frames = n / FRAME;
+    if (tid == 0) {
+        for (int s = 0; s < FLE_WSLOTS; ++s) {
+            mbar_init(&w_full[s], 1);
+            mbar_init(&w_free[s], FLE_PACK / 32);
+        }
+        for (int s = 0; s < FLE_PSLOTS; ++s) {
+            mbar_init(&p_full[s], 1);
+            mbar_init(&p_free[s], FLE_PACK / 32);
+        }
+        fence_mbar_init();
+    }
+    if (tid <= 8) {
+        const PackK k = make_pack_k(tid ? tid : 8);
+        ktab[tid] = tid ? make_uint4(k.k1, k.k2, k.k3, k.ra) : make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+
+    if (warp == FLE_PACK / 32) {
+        // ================================ service warp ===========================================
+        if (lane == 0) {
+            const uint64_t keep = l2_policy_evict_last(), drop = l2_policy_evict_first();
+            for (long long k = 0; k < iters; ++k) {
+                if (k < Kw) {  // first touch: from DRAM, stays in L2 for the pack touch FLE_LEAD iterations later
+                    const int s = (int)(k % FLE_WSLOTS);
+                    if (k >= FLE_WSLOTS) mbar_wait(&w_free[s], (uint32_t)(k / FLE_WSLOTS - 1) & 1u);
+                    const long long tile = c + k * G;
+                    const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tile);
+                    if (nfr) {
+                        mbar_expect_tx(&w_full[s], nfr * FRAME);
+                        tma_load_1d_hint(wbuf + s * FLE_TILE_BYTES, in + (size_t)tile * FLE_TILE_BYTES, nfr * FRAME, &w_full[s], keep);
+                    } else {
+                        mbar_arrive(&w_full[s]);
+                    }
+                }
+                const long long kp = k - FLE_LEAD;
+                if (kp >= 0) {  // second touch: an L2 hit, not needed afterwards
+                    const int s = (int)(kp % FLE_PSLOTS);
+                    if (kp >= FLE_PSLOTS) mbar_wait(&p_free[s], (uint32_t)(kp / FLE_PSLOTS - 1) & 1u);
+                    const long long tile = c + kp * G;
+                    const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tile);
+                    if (nfr) {
+                        mbar_expect_tx(&p_full[s], nfr * FRAME);
+                        tma_load_1d_hint(pbuf + s * FLE_TILE_BYTES, in + (size_t)tile * FLE_TILE_BYTES, nfr * FRAME, &p_full[s], drop);
+                    } else {
+                        mbar_arrive(&p_full[s]);
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ================================== pack warps =========================================
+    const int t = tid & 3;
+    const uint64_t drop = l2_policy_evict_first();
+    const int Kw_i = (int)Kw, iters_i = (int)iters;
+    int sw = 0, sp = 0, so = 0, mw = 0, mp = 0;  // slot of the width tile, the pack tile, their meta rows
+    uint32_t w_par = 0, p_par = 0;
+    for (int k = 0; k < iters_i; ++k) {
+        const bool doW = k < Kw_i;
+        const int kp = k - FLE_LEAD;
+        const bool doP = kp >= 0;
+        const long long tileW = c + (long long)k * G, tileP = c + (long long)kp * G;
+        uint8_t* const ptile = pbuf + sp * FLE_TILE_BYTES;
+        uint8_t* const otile = obuf + so * FLE_TILE_BYTES;
+        // the pack tile's first unit in `values`: posted FLE_LEAD * G tiles ago, asked for now and looked at after the barrier
+        uint64_t g = 1ull << 63;
+        if (doP && tileP > 0 && lane == 0) g = ld_relaxed_u64(inc + tileP);
+
+        // ---- width touch of tile W
+        if (doW) {
+            const int nfrW = fle_full_frames_of(full_frames, tileW);
+            mbar_wait(&w_full[sw], w_par);
+            const uint8_t* wt = wbuf + sw * FLE_TILE_BYTES;
+            // one thread per frame, no shuffles: the eight 16-byte pieces are read in an order rotated by the frame
+            // number, so the eight lanes of a quarter-warp hit eight different bank groups (frames are 128 bytes apart)
+            for (int fr = tid; fr < FLE_TILE_FRAMES; fr += FLE_PACK) {
+                const uint4* p = reinterpret_cast<const uint4*>(wt + fr * 128);
+                uint32_t o = 0;
+#if !(FLE_EXP & 2)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint4 a = p[(j + fr) & 7];  // frames past nfr read stale shared memory and get width 0
+                    o |= (a.x | a.y) | (a.z | a.w);
+                }
+                o |= o >> 16;
+                o |= o >> 8;
+#else
+                o = 1u << (fr & 7);
+#endif
+                sh.bw[k & 1][fr] = (uint8_t)((fr < nfrW) ? width_of_or(o) : 0u);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&w_free[sw]);  // the slot may be refilled
+        }
+        // ---- pack touch of tile P: the frames' bytes into registers
+        uint4 A[FLE_ITEMS], C[FLE_ITEMS];
+        if (doP) {
+            mbar_wait(&p_full[sp], p_par);
+#pragma unroll
+            for (int i = 0; i < FLE_ITEMS; ++i) {
+                const int fr = i * (FLE_PACK / 4) + (tid >> 2);
+                const uint4* p = reinterpret_cast<const uint4*>(ptile + fr * 128 + t * 32);
+                A[i] = p[0];
+                C[i] = p[1];
+            }
+            if (tid == 0) tma_store_wait_read<FLE_OSLOTS - 1>();  // the output slot's last bulk store has read it
+        }
+        bar_sync(BAR_P, FLE_PACK);  // #1: widths of tile W; the output slot is free
+        if (warp == 0 && doW) {
+            // widths -> `bits`, the tile's size to the scanner, (offset, width) of every frame kept for the pack touch
+            const int nfrW = fle_full_frames_of(full_frames, tileW);
+            const uint32_t v = reinterpret_cast<const uint32_t*>(sh.bw[k & 1])[lane];
+            const uint32_t b0 = v & 0xff, b1 = (v >> 8) & 0xff, b2 = (v >> 16) & 0xff, b3 = v >> 24;
+            const uint32_t s = b0 + b1 + b2 + b3;
+            uint32_t inc_s = s;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t o = __shfl_up_sync(0xffffffffu, inc_s, d);
+                if (lane >= d) inc_s += o;
+            }
+            const uint32_t ex = inc_s - s;
+            reinterpret_cast<uint4*>(sh.meta[mw])[lane] =
+                make_uint4(ex << 8 | b0, (ex + b0) << 8 | b1, (ex + b0 + b1) << 8 | b2, (ex + b0 + b1 + b2) << 8 | b3);
+            const size_t f0 = (size_t)tileW * FLE_TILE_FRAMES;
+            if (nfrW == FLE_TILE_FRAMES && (reinterpret_cast<uintptr_t>(bits) & 3) == 0) {
+                reinterpret_cast<uint32_t*>(bits + f0)[lane] = v;
+            } else {
+                for (int f = lane; f < nfrW; f += 32) bits[f0 + f] = sh.bw[k & 1][f];
+            }
+            if (lane == 31) {
+                sh.total[mw] = inc_s;
+                st_relaxed_u32(agg + tileW, 0x80000000u | inc_s);  // to the scanner
+            }
+        }
+        if (doW) {
+            if (++sw == FLE_WSLOTS) sw = 0, w_par ^= 1u;
+            if (++mw == FLE_LEAD + 1) mw = 0;
+        }
+        if (!doP) continue;
+        const uint32_t total = sh.total[mp];
+        if (lane == 0)
+            while ((g >> 63) == 0) {
+                __nanosleep(64);
+                g = ld_relaxed_u64(inc + tileP);
+            }
+        const uint64_t base = __shfl_sync(0xffffffffu, g, 0) & ~(1ull << 63);
+        {
+            const uint32_t tw = smem_u32(otile);
+#pragma unroll
+            for (int i = 0; i < FLE_ITEMS; ++i) {
+                const uint32_t m = sh.meta[mp][i * (FLE_PACK / 4) + (tid >> 2)];
+                const uint32_t b = m & 0xffu;  // 0 for frames past the end: every store below is predicated off
+                const uint4 kk = ktab[b];
+                PackK pk;
+                pk.k1 = kk.x; pk.k2 = kk.y; pk.k3 = kk.z; pk.ra = kk.w; pk.s8 = 8 * b;
+                const uint32_t w = tw + ((m >> 8) * 4u + b * t) * 4u;
+                const uint32_t a[4] = {A[i].x, A[i].y, A[i].z, A[i].w};
+                const uint32_t c4[4] = {C[i].x, C[i].y, C[i].z, C[i].w};
+#if (FLE_EXP & 1)
+                if (b == 77) sts32_pred(w, a[0] ^ c4[0] ^ a[1] ^ c4[1] ^ a[2] ^ c4[2] ^ a[3] ^ c4[3] ^ pk.k1, true);
+#else
+                pack32_store(a, c4, b, pk, [&](bool p, uint32_t j, uint32_t v) { sts32_pred(w + 4u * j, v, p); });
+#endif
+            }
+        }
+        // every shared-memory read of the staged tile has returned (its values were used above): the slot may be refilled.
+        // (Not earlier: an arrive right behind the loads can overtake them.)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_free[sp]);
+        fence_proxy_async_smem();  // the packed tile is read by a bulk store
+        bar_sync(BAR_P, FLE_PACK);  // #2: packed
+        if (tid == 0) {
+            if (total) tma_store_1d_hint(values + base * 16, otile, total * 16, drop);
+            tma_store_commit();  // (an empty group for an empty tile keeps the group count in step with kp)
+        }
+        if (tileP == tiles - 1) {
+            // ---- the partial frame and the total size: this CTA owns the last tile
+            const uint32_t tail = (uint32_t)(n % FRAME);
+            uint64_t vsize = (base + total) * 16;
+            if (tail) vsize += fle_tail_frame(in + full_frames * FRAME, tail, bits + full_frames, values + vsize, tail_scratch);
+            if (tid == 0) *values_size = vsize;
+        }
+        if (++sp == FLE_PSLOTS) sp = 0, p_par ^= 1u;
+        if (++so == FLE_OSLOTS) so = 0;
+        if (++mp == FLE_LEAD + 1) mp = 0;
+    }
+    if (tid == 0) tma_store_wait_read<0>();  // shared memory must outlive the bulk stores' reads
+}
+
+// =============================================================================================
+//                                        launcher
+// =============================================================================================
+static size_t fle_tiles_padded(size_t n) { return (fl_tiles(n) + 255) / 256 * 256; }  // whole scanner chunks
+// workspace: inc[tiles] u64 | agg[tiles] u32
+size_t fl_encode_workspace_bytes(size_t n) { return fle_tiles_padded(n) * 12 + 16; }
+
+cudaError_t fl_encode_launch(const uint8_t* d_in, size_t n, uint8_t* d_bits, uint8_t* d_values, uint64_t* d_values_size,
+                             void* d_ws, cudaStream_t stream)
+{
+    const size_t tiles = fl_tiles(n), tmax = fle_tiles_padded(n);
+    uint64_t* inc = reinterpret_cast<uint64_t*>(d_ws);
+    uint32_t* agg = reinterpret_cast<uint32_t*>(inc + tmax);
+    cudaError_t e = cudaMemsetAsync(d_ws, 0, fl_encode_workspace_bytes(n), stream);
+    if (e != cudaSuccess) return e;
+    constexpr int smem = (FLE_WSLOTS + FLE_PSLOTS + FLE_OSLOTS) * FLE_TILE_BYTES;
+    // the grid must be fully co-resident: the pack touch waits for the scanner CTA, the scanner for every width touch
+    int dev = 0;
+    e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    static int resident[64];
+    int cap = dev < 64 ? resident[dev] : 0;
+    if (!cap) {
+        e = cudaFuncSetAttribute((const void*)fl_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        int sms = 0, per_sm = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)fl_encode_kernel, FLE_THREADS, smem);
+        if (e != cudaSuccess) return e;
+        if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+        cap = sms * std::max(1, std::min(per_sm, FLE_CTAS));
+        if (cap < 2) return cudaErrorLaunchOutOfResources;
+        if (dev < 64) resident[dev] = cap;
+    }
+    const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap - 1) + 1;  // the scanner CTA + the workers
+    fl_encode_kernel<<<grid, FLE_THREADS, smem, stream>>>(d_in, n, d_bits, d_values, d_values_size, inc, agg, (long long)tiles);
+    return cudaGetLastError();
+}
+
+}  // namespace flrl
