@@ -237,6 +237,13 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
 #pragma unroll
                 for (int j = 0; j < 5; ++j) g[i][j] = w[q + j];
             }
+            {
+                uint32_t x = 0;
+#pragma unroll
+                for (int i = 0; i < FLD_ITEMS; ++i)
+                    x ^= (r[i][0] ^ r[i][1] ^ r[i][2]) ^ (r[i][3] ^ g[i][0] ^ g[i][1]) ^ (g[i][2] ^ g[i][3] ^ g[i][4]);
+                loads_landed(x);
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive(&freeb[s]);  // everything this warp needs from the stage is in registers
             uint8_t* otile = out + (size_t)(t0 + k) * FLD_TILE_BYTES;

@@ -97,11 +97,11 @@ FLRL_HD uint32_t width_of_or(uint32_t or8)
     return w ? w : 1u;
 }
 
-// Per-frame constants of the multiply-based packer; all are 0 for b == 8 (identity).
+// Per-frame constants of the multiply-based packer; for b == 8 the multipliers are 0, 0, 1 and the shift 0 (identity).
 struct PackK {
     uint32_t k1;  // 2^(8-b)   - 1 : bytes   -> 2b-bit pairs in 16-bit lanes (left aligned)
     uint32_t k2;  // 2^(16-2b) - 1 : pairs   -> 4b-bit quads in 32-bit words
-    uint32_t k3;  // 2^(32-4b) - 1 : quads   -> 8b-bit octets in 64-bit words
+    uint32_t k3;  // 2^(32-4b)     : quads   -> 8b-bit octets in 64-bit words
     uint32_t ra;  // 56 - 7b      : right-align shift of an octet
     uint32_t s8;  // 8b
 };
@@ -110,28 +110,23 @@ FLRL_HD PackK make_pack_k(uint32_t b)
     PackK k;
     k.k1 = (1u << (8 - b)) - 1u;
     k.k2 = (1u << (16 - 2 * b)) - 1u;
-    k.k3 = (1u << (32 - 4 * b)) - 1u;
+    k.k3 = 1u << (32 - 4 * b);
     k.ra = 56 - 7 * b;
     k.s8 = 8 * b;
     return k;
 }
 
-// octet = (c1:c0) + c0 * k3 : one IMAD.WIDE.U32 whose addend is the register pair (c0, c1)
+// octet = c0 * k3 + (c1 << 32): one IMAD.WIDE.U32 and one add into its high word (no carry: the low word is the product's)
 FLRL_HD uint64_t pack_octet(uint32_t c0, uint32_t c1, uint32_t k3)
 {
-#if defined(__CUDA_ARCH__)
-    uint64_t r;
-    asm("{\n\t.reg .b64 t;\n\tmov.b64 t, {%1, %2};\n\tmad.wide.u32 %0, %1, %3, t;\n\t}" : "=l"(r) : "r"(c0), "r"(c1), "r"(k3));
-    return r;
-#else
-    return (((uint64_t)c1 << 32) | c0) + (uint64_t)c0 * k3;
-#endif
+    const uint64_t m = (uint64_t)c0 * k3;
+    return (m & 0xffffffffull) | ((uint64_t)((uint32_t)(m >> 32) + c1) << 32);
 }
 
 // 16 input bytes (x[0..3], little endian) of width b -> 16b bits, right aligned in (lo,hi).
 //   stage 1: t  = x + (x & 0x00ff00ff) * k1   -> pair (v0 + v1<<b) at bits [8-b, 8+b) of each half
 //   stage 2: c  = t + (t & 0x0000ffff) * k2   -> quad at bits [24-3b, 24+b)
-//   stage 3: W  = (c1:c0) + c0 * k3           -> octet at bits [56-7b, 56+b)
+//   stage 3: W  = (c1 << 32) + c0 * k3        -> octet at bits [56-7b, 56+b)
 //   stage 4: Q  = P0 | P1 << 8b               (P = W >> (56-7b))
 FLRL_HD void pack16(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, const PackK& k, uint64_t& qlo, uint64_t& qhi)
 {
