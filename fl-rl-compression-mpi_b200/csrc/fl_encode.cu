@@ -15,12 +15,15 @@
 //     (offset, width) from the ring, the tile's offset in `values` (posted thousands of tiles ago: one load, asked
 //     for at the top of the iteration), lane-local multiply/shift packing (flrl_bits.cuh; fl_cpu.cu:64-84; four
 //     lanes per frame) into an output slot, one TMA bulk store (every tile starts on a 16-byte boundary of `values`).
-// FLE_LEAD * G tiles (~45 MiB) exceed everything in flight and stay inside the 126 MB L2, so no CTA ever waits for
-// another one.  The service warp refills a slot as soon as its last reader is done; two named barriers per iteration.
+// FLE_LEAD * G tiles (~19 MiB) exceed what is in flight and stay inside the 126 MB L2 (a longer lead loses more of
+// the second touches to L2 misses).  The pack warps never wait for each other: everything that joins them — loads,
+// the scan of a tile's widths, the bulk store — goes through the service warp (bar.arrive from the pack warps,
+// bar.sync in the service warp), and the pack warps wait only on mbarriers for data: a loaded slot, a free output slot.
 // The kernel is bound by instruction issue and latency in the pack warps (about 1000 instructions per warp and tile,
 // ~450 of them the packing), not by memory: without the packing arithmetic it runs at 86 % of the HBM bandwidth.
-// (History: one CTA per tile with a look-back, 0.417 ms / GiB; this structure with widths by shuffles and recomputed
-// in the pack touch, 0.42 ms; widths by one thread per frame + the (offset, width) ring, 0.36 ms.)
+// (History: one CTA per tile with a look-back, 0.417 ms / GiB; persistent two-touch with widths by shuffles and
+// recomputed in the pack touch, 0.42 ms; widths by one thread per frame + the (offset, width) ring, 0.36 ms; joins
+// moved to the service warp and a lead of 2 iterations, 0.33 ms.)
 //
 // The grid must be fully co-resident (tiles are assigned statically): the launcher sizes it from the occupancy API.
 //
@@ -58,12 +61,14 @@ static constexpr int FLE_ITEMS = 4 * FLE_TILE_FRAMES / FLE_PACK;  // 32-byte ite
 #define FLE_CTAS 4  // per SM
 #endif
 #ifndef FLE_LEAD
-#define FLE_LEAD 5  // iterations between the two touches of a tile
+#define FLE_LEAD 2  // iterations between the two touches of a tile (1: 0.370 ms, 2: 0.328, 3: 0.337, 5: 0.356)
 #endif
 #ifndef FLE_EXP
 #define FLE_EXP 0  // timing experiments only (wrong output): 1 = no packing arithmetic, 2 = no width arithmetic
 #endif
-static constexpr uint32_t BAR_P = 1;  // named barrier of the pack warps
+static constexpr uint32_t BAR_P = 1;  // named barriers: the pack warps among themselves (tail frame only),
+static constexpr uint32_t BAR_W = 2;  //   widths of a tile ready: pack warps arrive, the service warp waits,
+static constexpr uint32_t BAR_O = 3;  //   a tile is packed: pack warps arrive, the service warp waits
 
 struct FleShared {
     uint8_t bw[2][FLE_TILE_FRAMES];  // width touch: widths (two copies: warp 0 reads one while the others fill the next)
@@ -114,7 +119,8 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
     uint8_t* const wbuf = smem;                                 // FLE_WSLOTS x 16 KiB: width touch
     uint8_t* const pbuf = smem + FLE_WSLOTS * FLE_TILE_BYTES;   // FLE_PSLOTS x 16 KiB: pack touch
     uint8_t* const obuf = pbuf + FLE_PSLOTS * FLE_TILE_BYTES;   // FLE_OSLOTS x 16 KiB: the packed tile, source of the bulk store
-    __shared__ __align__(8) uint64_t w_full[FLE_WSLOTS], w_free[FLE_WSLOTS], p_full[FLE_PSLOTS], p_free[FLE_PSLOTS];
+    __shared__ __align__(8) uint64_t w_full[FLE_WSLOTS], w_free[FLE_WSLOTS], p_full[FLE_PSLOTS], p_free[FLE_PSLOTS],
+        o_free[FLE_OSLOTS];
     __shared__ FleShared sh;
     __shared__ __align__(16) uint4 ktab[9];  // PackK{k1,k2,k3,ra} per width
     __shared__ uint32_t tail_scratch[36];
@@ -125,8 +131,8 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
         return;
     }
     const long long G = gridDim.x - 1, c = blockIdx.x - 1;
-    const long long Kw = (tiles - c + G - 1) / G;  // tiles of this CTA: c, c + G, ...
-    const long long iters = Kw + FLE_LEAD;
+    const int Kw = (int)((tiles - c + G - 1) / G);  // tiles of this CTA: c, c + G, ...
+    const int iters = Kw + FLE_LEAD;
     const size_t full_frames = n / FRAME;
     if (tid == 0) {
         for (int s = 0; s < FLE_WSLOTS; ++s) {
@@ -137,6 +143,7 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
             mbar_init(&p_full[s], 1);
             mbar_init(&p_free[s], FLE_PACK / 32);
         }
+        for (int s = 0; s < FLE_OSLOTS; ++s) mbar_init(&o_free[s], 1);
         fence_mbar_init();
     }
     if (tid <= 8) {
@@ -147,60 +154,114 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
 
     if (warp == FLE_PACK / 32) {
         // ================================ service warp ===========================================
-        if (lane == 0) {
-            const uint64_t keep = l2_policy_evict_last(), drop = l2_policy_evict_first();
-            for (long long k = 0; k < iters; ++k) {
-                if (k < Kw) {  // first touch: from DRAM, stays in L2 for the pack touch FLE_LEAD iterations later
-                    const int s = (int)(k % FLE_WSLOTS);
-                    if (k >= FLE_WSLOTS) mbar_wait(&w_free[s], (uint32_t)(k / FLE_WSLOTS - 1) & 1u);
-                    const long long tile = c + k * G;
-                    const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tile);
-                    if (nfr) {
-                        mbar_expect_tx(&w_full[s], nfr * FRAME);
-                        tma_load_1d_hint(wbuf + s * FLE_TILE_BYTES, in + (size_t)tile * FLE_TILE_BYTES, nfr * FRAME, &w_full[s], keep);
-                    } else {
-                        mbar_arrive(&w_full[s]);
-                    }
+        // Everything that joins the four pack warps goes through this warp, so that they never wait for each other:
+        //   loads (both touches), the per-tile scan of the widths (bits, (offset, width) ring, size to the scanner),
+        //   the bulk store of a packed tile.  Order per iteration k:  P load(k - LEAD) | widths(k) | W load(k + 1) | store(k - LEAD)
+        const uint64_t keep = l2_policy_evict_last(), drop = l2_policy_evict_first();
+        auto load_w = [&](int k) {  // refill a width slot with tile c + k G: first touch, stays in L2 for the second one
+            const int sw = k % FLE_WSLOTS;
+            if (k >= FLE_WSLOTS) mbar_wait(&w_free[sw], (uint32_t)(k / FLE_WSLOTS - 1) & 1u);
+            if (lane == 0) {
+                const long long tile = c + (long long)k * G;
+                const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tile);
+                if (nfr) {
+                    mbar_expect_tx(&w_full[sw], nfr * FRAME);
+                    tma_load_1d_hint(wbuf + sw * FLE_TILE_BYTES, in + (size_t)tile * FLE_TILE_BYTES, nfr * FRAME, &w_full[sw], keep);
+                } else {
+                    mbar_arrive(&w_full[sw]);
                 }
-                const long long kp = k - FLE_LEAD;
-                if (kp >= 0) {  // second touch: an L2 hit, not needed afterwards
-                    const int s = (int)(kp % FLE_PSLOTS);
-                    if (kp >= FLE_PSLOTS) mbar_wait(&p_free[s], (uint32_t)(kp / FLE_PSLOTS - 1) & 1u);
-                    const long long tile = c + kp * G;
-                    const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tile);
+            }
+            __syncwarp();
+        };
+        if (Kw > 0) load_w(0);
+        for (int k = 0; k < iters; ++k) {
+            const bool doW = k < Kw;
+            const int kp = k - FLE_LEAD;
+            const bool doP = kp >= 0;
+            const long long tileW = c + (long long)k * G, tileP = c + (long long)kp * G;
+            uint64_t g = 1ull << 63;
+            if (doP) {  // second touch: an L2 hit, not needed afterwards
+                const int sp = kp % FLE_PSLOTS;
+                if (kp >= FLE_PSLOTS) mbar_wait(&p_free[sp], (uint32_t)(kp / FLE_PSLOTS - 1) & 1u);
+                if (lane == 0) {
+                    const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tileP);
                     if (nfr) {
-                        mbar_expect_tx(&p_full[s], nfr * FRAME);
-                        tma_load_1d_hint(pbuf + s * FLE_TILE_BYTES, in + (size_t)tile * FLE_TILE_BYTES, nfr * FRAME, &p_full[s], drop);
+                        mbar_expect_tx(&p_full[sp], nfr * FRAME);
+                        tma_load_1d_hint(pbuf + sp * FLE_TILE_BYTES, in + (size_t)tileP * FLE_TILE_BYTES, nfr * FRAME, &p_full[sp], drop);
                     } else {
-                        mbar_arrive(&p_full[s]);
+                        mbar_arrive(&p_full[sp]);
                     }
+                    // the tile's first unit in `values`: posted FLE_LEAD * G tiles ago, asked for now, used at the store
+                    if (tileP > 0) g = ld_relaxed_u64(inc + tileP);
                 }
+                __syncwarp();
+            }
+            if (doW) {
+                // widths of tile W (written by the pack warps) -> `bits`, the tile's size to the scanner, (offset, width)
+                // of every frame kept for the pack touch
+                const int mw = k % (FLE_LEAD + 1);
+                bar_sync(BAR_W, FLE_THREADS);
+                const int nfrW = fle_full_frames_of(full_frames, tileW);
+                const uint32_t v = reinterpret_cast<const uint32_t*>(sh.bw[k & 1])[lane];
+                const uint32_t b0 = v & 0xff, b1 = (v >> 8) & 0xff, b2 = (v >> 16) & 0xff, b3 = v >> 24;
+                const uint32_t s = b0 + b1 + b2 + b3;
+                uint32_t inc_s = s;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xffffffffu, inc_s, d);
+                    if (lane >= d) inc_s += o;
+                }
+                const uint32_t ex = inc_s - s;
+                reinterpret_cast<uint4*>(sh.meta[mw])[lane] =
+                    make_uint4(ex << 8 | b0, (ex + b0) << 8 | b1, (ex + b0 + b1) << 8 | b2, (ex + b0 + b1 + b2) << 8 | b3);
+                const size_t f0 = (size_t)tileW * FLE_TILE_FRAMES;
+                if (nfrW == FLE_TILE_FRAMES && (reinterpret_cast<uintptr_t>(bits) & 3) == 0) {
+                    reinterpret_cast<uint32_t*>(bits + f0)[lane] = v;
+                } else {
+                    for (int f = lane; f < nfrW; f += 32) bits[f0 + f] = sh.bw[k & 1][f];
+                }
+                if (lane == 31) {
+                    sh.total[mw] = inc_s;
+                    st_relaxed_u32(agg + tileW, 0x80000000u | inc_s);  // to the scanner
+                }
+                __syncwarp();  // the ring row is complete before lane 0 hands out the pack touch of this tile
+                if (k + 1 < Kw) load_w(k + 1);  // its slot was released before the pack warps arrived at the barrier above
+            }
+            if (doP) {
+                const int so = kp % FLE_OSLOTS, mp = kp % (FLE_LEAD + 1);
+                bar_sync(BAR_O, FLE_THREADS);  // tile P is packed (and fenced for the bulk store)
+                if (lane == 0) {
+                    while ((g >> 63) == 0) {
+                        __nanosleep(64);
+                        g = ld_relaxed_u64(inc + tileP);
+                    }
+                    const uint64_t base = g & ~(1ull << 63);
+                    const uint32_t total = sh.total[mp];
+                    if (total) tma_store_1d_hint(values + base * 16, obuf + so * FLE_TILE_BYTES, total * 16, drop);
+                    tma_store_commit();
+                    tma_store_wait_read<0>();
+                    mbar_arrive(&o_free[so]);  // the output slot may be written again
+                }
+                __syncwarp();
             }
         }
         return;
     }
 
     // ================================== pack warps =========================================
+    // They wait only for data: a loaded slot, a free output slot.  What they produce for others they hand over with
+    // bar.arrive, never waiting for each other.
     const int t = tid & 3;
-    const uint64_t drop = l2_policy_evict_first();
-    const int Kw_i = (int)Kw, iters_i = (int)iters;
-    int sw = 0, sp = 0, so = 0, mw = 0, mp = 0;  // slot of the width tile, the pack tile, their meta rows
-    uint32_t w_par = 0, p_par = 0;
-    for (int k = 0; k < iters_i; ++k) {
-        const bool doW = k < Kw_i;
+    for (int k = 0; k < iters; ++k) {
+        const bool doW = k < Kw;
         const int kp = k - FLE_LEAD;
-        const bool doP = kp >= 0;
         const long long tileW = c + (long long)k * G, tileP = c + (long long)kp * G;
-        uint8_t* const ptile = pbuf + sp * FLE_TILE_BYTES;
-        uint8_t* const otile = obuf + so * FLE_TILE_BYTES;
-        // the pack tile's first unit in `values`: posted FLE_LEAD * G tiles ago, asked for now and looked at after the barrier
-        uint64_t g = 1ull << 63;
-        if (doP && tileP > 0 && lane == 0) g = ld_relaxed_u64(inc + tileP);
 
         // ---- width touch of tile W
         if (doW) {
+            const int sw = k % FLE_WSLOTS;
             const int nfrW = fle_full_frames_of(full_frames, tileW);
-            mbar_wait(&w_full[sw], w_par);
+            mbar_wait(&w_full[sw], (uint32_t)(k / FLE_WSLOTS) & 1u);
             const uint8_t* wt = wbuf + sw * FLE_TILE_BYTES;
             // one thread per frame, no shuffles: the eight 16-byte pieces are read in an order rotated by the frame
             // number, so the eight lanes of a quarter-warp hit eight different bank groups (frames are 128 bytes apart)
@@ -221,70 +282,35 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
                 sh.bw[k & 1][fr] = (uint8_t)((fr < nfrW) ? width_of_or(o) : 0u);
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(&w_free[sw]);  // the slot may be refilled
+            if (lane == 0) mbar_arrive(&w_free[sw]);  // the slot may be refilled (its values were used above)
+            bar_arrive(BAR_W, FLE_THREADS);           // the widths are in shared memory: over to the service warp
         }
-        // ---- pack touch of tile P: the frames' bytes into registers
+        if (kp < 0) continue;
+
+        // ---- pack touch of tile P
+        const int sp = kp % FLE_PSLOTS, so = kp % FLE_OSLOTS, mp = kp % (FLE_LEAD + 1);
+        const uint8_t* ptile = pbuf + sp * FLE_TILE_BYTES;
+        mbar_wait(&p_full[sp], (uint32_t)(kp / FLE_PSLOTS) & 1u);  // (also: the tile's ring row is complete)
         uint4 A[FLE_ITEMS], C[FLE_ITEMS];
-        if (doP) {
-            mbar_wait(&p_full[sp], p_par);
+        uint32_t M[FLE_ITEMS];
 #pragma unroll
-            for (int i = 0; i < FLE_ITEMS; ++i) {
-                const int fr = i * (FLE_PACK / 4) + (tid >> 2);
-                const uint4* p = reinterpret_cast<const uint4*>(ptile + fr * 128 + t * 32);
-                A[i] = p[0];
-                C[i] = p[1];
-            }
-            if (tid == 0) tma_store_wait_read<FLE_OSLOTS - 1>();  // the output slot's last bulk store has read it
+        for (int i = 0; i < FLE_ITEMS; ++i) {
+            const int fr = i * (FLE_PACK / 4) + (tid >> 2);
+            const uint4* p = reinterpret_cast<const uint4*>(ptile + fr * 128 + t * 32);
+            A[i] = p[0];
+            C[i] = p[1];
+            M[i] = sh.meta[mp][fr];  // (offset in 16-byte units) << 8 | width
         }
-        bar_sync(BAR_P, FLE_PACK);  // #1: widths of tile W; the output slot is free
-        if (warp == 0 && doW) {
-            // widths -> `bits`, the tile's size to the scanner, (offset, width) of every frame kept for the pack touch
-            const int nfrW = fle_full_frames_of(full_frames, tileW);
-            const uint32_t v = reinterpret_cast<const uint32_t*>(sh.bw[k & 1])[lane];
-            const uint32_t b0 = v & 0xff, b1 = (v >> 8) & 0xff, b2 = (v >> 16) & 0xff, b3 = v >> 24;
-            const uint32_t s = b0 + b1 + b2 + b3;
-            uint32_t inc_s = s;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t o = __shfl_up_sync(0xffffffffu, inc_s, d);
-                if (lane >= d) inc_s += o;
-            }
-            const uint32_t ex = inc_s - s;
-            reinterpret_cast<uint4*>(sh.meta[mw])[lane] =
-                make_uint4(ex << 8 | b0, (ex + b0) << 8 | b1, (ex + b0 + b1) << 8 | b2, (ex + b0 + b1 + b2) << 8 | b3);
-            const size_t f0 = (size_t)tileW * FLE_TILE_FRAMES;
-            if (nfrW == FLE_TILE_FRAMES && (reinterpret_cast<uintptr_t>(bits) & 3) == 0) {
-                reinterpret_cast<uint32_t*>(bits + f0)[lane] = v;
-            } else {
-                for (int f = lane; f < nfrW; f += 32) bits[f0 + f] = sh.bw[k & 1][f];
-            }
-            if (lane == 31) {
-                sh.total[mw] = inc_s;
-                st_relaxed_u32(agg + tileW, 0x80000000u | inc_s);  // to the scanner
-            }
-        }
-        if (doW) {
-            if (++sw == FLE_WSLOTS) sw = 0, w_par ^= 1u;
-            if (++mw == FLE_LEAD + 1) mw = 0;
-        }
-        if (!doP) continue;
-        const uint32_t total = sh.total[mp];
-        if (lane == 0)
-            while ((g >> 63) == 0) {
-                __nanosleep(64);
-                g = ld_relaxed_u64(inc + tileP);
-            }
-        const uint64_t base = __shfl_sync(0xffffffffu, g, 0) & ~(1ull << 63);
+        if (kp >= FLE_OSLOTS) mbar_wait(&o_free[so], (uint32_t)(kp / FLE_OSLOTS - 1) & 1u);  // its last bulk store has read it
         {
-            const uint32_t tw = smem_u32(otile);
+            const uint32_t tw = smem_u32(obuf + so * FLE_TILE_BYTES);
 #pragma unroll
             for (int i = 0; i < FLE_ITEMS; ++i) {
-                const uint32_t m = sh.meta[mp][i * (FLE_PACK / 4) + (tid >> 2)];
-                const uint32_t b = m & 0xffu;  // 0 for frames past the end: every store below is predicated off
+                const uint32_t b = M[i] & 0xffu;  // 0 for frames past the end: every store below is predicated off
                 const uint4 kk = ktab[b];
                 PackK pk;
                 pk.k1 = kk.x; pk.k2 = kk.y; pk.k3 = kk.z; pk.ra = kk.w; pk.s8 = 8 * b;
-                const uint32_t w = tw + ((m >> 8) * 4u + b * t) * 4u;
+                const uint32_t w = tw + ((M[i] >> 8) * 4u + b * t) * 4u;
                 const uint32_t a[4] = {A[i].x, A[i].y, A[i].z, A[i].w};
                 const uint32_t c4[4] = {C[i].x, C[i].y, C[i].z, C[i].w};
 #if (FLE_EXP & 1)
@@ -298,24 +324,20 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
         // (Not earlier: an arrive right behind the loads can overtake them.)
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_free[sp]);
-        fence_proxy_async_smem();  // the packed tile is read by a bulk store
-        bar_sync(BAR_P, FLE_PACK);  // #2: packed
-        if (tid == 0) {
-            if (total) tma_store_1d_hint(values + base * 16, otile, total * 16, drop);
-            tma_store_commit();  // (an empty group for an empty tile keeps the group count in step with kp)
-        }
+        fence_proxy_async_smem();          // the packed tile is read by a bulk store
+        bar_arrive(BAR_O, FLE_THREADS);    // over to the service warp, which stores it
+
         if (tileP == tiles - 1) {
             // ---- the partial frame and the total size: this CTA owns the last tile
+            uint64_t g = 1ull << 63;
+            if (tileP > 0)
+                while (((g = ld_relaxed_u64(inc + tileP)) >> 63) == 0) __nanosleep(64);
             const uint32_t tail = (uint32_t)(n % FRAME);
-            uint64_t vsize = (base + total) * 16;
+            uint64_t vsize = ((g & ~(1ull << 63)) + sh.total[mp]) * 16;
             if (tail) vsize += fle_tail_frame(in + full_frames * FRAME, tail, bits + full_frames, values + vsize, tail_scratch);
             if (tid == 0) *values_size = vsize;
         }
-        if (++sp == FLE_PSLOTS) sp = 0, p_par ^= 1u;
-        if (++so == FLE_OSLOTS) so = 0;
-        if (++mp == FLE_LEAD + 1) mp = 0;
     }
-    if (tid == 0) tma_store_wait_read<0>();  // shared memory must outlive the bulk stores' reads
 }
 
 // =============================================================================================
