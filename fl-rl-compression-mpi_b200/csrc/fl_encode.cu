@@ -4,7 +4,7 @@
 // (/root/reference/src/fl/fl_gpu.cu:648-726, :758-808).
 //
 // The value offset of a tile needs the widths of every earlier tile.  Two touches per 128-frame tile (16 KiB),
-// FLE_LEAD iterations apart, by PERSISTENT CTAs (CTA c owns tiles c, c + G, c + 2G, ...; 4 pack warps + 1 service warp):
+// FLE_LEAD iterations apart, by PERSISTENT CTAs (4 pack warps + 1 service warp; tiles from an atomic counter):
 //   * width touch of tile t (first touch: DRAM -> L2 -> shared memory, L2 evict-last): per-frame width from the OR
 //     of the frame (fl_cpu.cu:37-50) — one thread per frame, its eight 16-byte pieces read in a rotated order so
 //     that a quarter-warp covers all banks, no shuffles.  Warp 0 writes the 128 widths to `bits`, scans them once,
@@ -25,7 +25,8 @@
 // recomputed in the pack touch, 0.42 ms; widths by one thread per frame + the (offset, width) ring, 0.36 ms; joins
 // moved to the service warp and a lead of 2 iterations, 0.33 ms.)
 //
-// The grid must be fully co-resident (tiles are assigned statically): the launcher sizes it from the occupancy API.
+// Tiles are handed out by an atomic counter (as in the run-length kernels): only running CTAs own tiles, so nothing
+// depends on the whole grid being resident; the launcher still sizes the grid to what fits, plus the scanner CTA.
 //
 // Only the final partial frame (n % 128 != 0) goes through a small cooperative scalar path in the CTA that
 // owns the last tile, which also publishes the total value size.
@@ -66,6 +67,7 @@ static constexpr int FLE_ITEMS = 4 * FLE_TILE_FRAMES / FLE_PACK;  // 32-byte ite
 #ifndef FLE_EXP
 #define FLE_EXP 0  // timing experiments only (wrong output): 1 = no packing arithmetic, 2 = no width arithmetic
 #endif
+static constexpr int FLE_IDS = FLE_LEAD + 3;
 static constexpr uint32_t BAR_P = 1;  // named barriers: the pack warps among themselves (tail frame only),
 static constexpr uint32_t BAR_W = 2;  //   widths of a tile ready: pack warps arrive, the service warp waits,
 static constexpr uint32_t BAR_O = 3;  //   a tile is packed: pack warps arrive, the service warp waits
@@ -75,6 +77,7 @@ struct FleShared {
     // kept from the width touch to the pack touch FLE_LEAD iterations later: per frame (offset in 16-byte units) << 8 | width
     __align__(16) uint32_t meta[FLE_LEAD + 1][FLE_TILE_FRAMES];
     uint32_t total[FLE_LEAD + 1];    // packed size of the tile (16-byte units)
+    int tile[FLE_LEAD + 3];          // tile of iteration k at [k % FLE_IDS], from its first load to its store
 };
 
 __device__ __forceinline__ uint32_t fle_byte_sum(uint32_t v) { return __dp4a(v, 0x01010101u, 0u); }
@@ -113,7 +116,8 @@ __device__ __forceinline__ int fle_full_frames_of(size_t full_frames, long long 
 
 __global__ void __launch_bounds__(FLE_THREADS, FLE_CTAS)
 fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__ bits, uint8_t* __restrict__ values,
-                 uint64_t* __restrict__ values_size, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg, long long tiles)
+                 uint64_t* __restrict__ values_size, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg,
+                 unsigned int* __restrict__ next_tile, long long tiles)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* const wbuf = smem;                                 // FLE_WSLOTS x 16 KiB: width touch
@@ -130,9 +134,10 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
         if (warp == 0) scan_pair_counts(agg, inc, tiles, lane);
         return;
     }
-    const long long G = gridDim.x - 1, c = blockIdx.x - 1;
-    const int Kw = (int)((tiles - c + G - 1) / G);  // tiles of this CTA: c, c + G, ...
-    const int iters = Kw + FLE_LEAD;
+    // Tiles are handed out by an atomic counter, in the order the CTAs ask: a tile is only ever waited for by CTAs that
+    // run, and its owner runs too (no co-residency needed), and the scanner sees sizes posted roughly in tile order.
+    // sh.tile[k % FLE_IDS] is the tile of this CTA's iteration k (-1: there was none left).
+    int Kw = 1 << 30;  // number of tiles this CTA got: known when the counter runs out
     const size_t full_frames = n / FRAME;
     if (tid == 0) {
         for (int s = 0; s < FLE_WSLOTS; ++s) {
@@ -158,27 +163,33 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
         //   loads (both touches), the per-tile scan of the widths (bits, (offset, width) ring, size to the scanner),
         //   the bulk store of a packed tile.  Order per iteration k:  P load(k - LEAD) | widths(k) | W load(k + 1) | store(k - LEAD)
         const uint64_t keep = l2_policy_evict_last(), drop = l2_policy_evict_first();
-        auto load_w = [&](int k) {  // refill a width slot with tile c + k G: first touch, stays in L2 for the second one
+        unsigned int idn = 0;  // lane 0: the tile of the next width load, asked for one iteration ahead
+        if (lane == 0) idn = atomicAdd(next_tile, 1u);
+        auto load_w = [&](int k) {  // refill a width slot with this CTA's k-th tile: first touch, stays in L2 for the second one
             const int sw = k % FLE_WSLOTS;
             if (k >= FLE_WSLOTS) mbar_wait(&w_free[sw], (uint32_t)(k / FLE_WSLOTS - 1) & 1u);
+            const unsigned int id = __shfl_sync(0xffffffffu, idn, 0);
+            const bool none = (long long)id >= tiles;
             if (lane == 0) {
-                const long long tile = c + (long long)k * G;
-                const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tile);
+                sh.tile[k % FLE_IDS] = none ? -1 : (int)id;  // (published by the arrive / expect_tx below)
+                const uint32_t nfr = none ? 0u : (uint32_t)fle_full_frames_of(full_frames, id);
                 if (nfr) {
                     mbar_expect_tx(&w_full[sw], nfr * FRAME);
-                    tma_load_1d_hint(wbuf + sw * FLE_TILE_BYTES, in + (size_t)tile * FLE_TILE_BYTES, nfr * FRAME, &w_full[sw], keep);
+                    tma_load_1d_hint(wbuf + sw * FLE_TILE_BYTES, in + (size_t)id * FLE_TILE_BYTES, nfr * FRAME, &w_full[sw], keep);
                 } else {
                     mbar_arrive(&w_full[sw]);
                 }
+                if (!none) idn = atomicAdd(next_tile, 1u);
             }
             __syncwarp();
+            if (none) Kw = k;
         };
-        if (Kw > 0) load_w(0);
-        for (int k = 0; k < iters; ++k) {
+        load_w(0);
+        for (int k = 0; k < Kw + FLE_LEAD; ++k) {
             const bool doW = k < Kw;
             const int kp = k - FLE_LEAD;
             const bool doP = kp >= 0;
-            const long long tileW = c + (long long)k * G, tileP = c + (long long)kp * G;
+            const long long tileW = doW ? sh.tile[k % FLE_IDS] : -1, tileP = doP ? sh.tile[kp % FLE_IDS] : -1;
             uint64_t g = 1ull << 63;
             if (doP) {  // second touch: an L2 hit, not needed afterwards
                 const int sp = kp % FLE_PSLOTS;
@@ -225,7 +236,7 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
                     st_relaxed_u32(agg + tileW, 0x80000000u | inc_s);  // to the scanner
                 }
                 __syncwarp();  // the ring row is complete before lane 0 hands out the pack touch of this tile
-                if (k + 1 < Kw) load_w(k + 1);  // its slot was released before the pack warps arrived at the barrier above
+                load_w(k + 1);  // its slot was released before the pack warps arrived at the barrier above
             }
             if (doP) {
                 const int so = kp % FLE_OSLOTS, mp = kp % (FLE_LEAD + 1);
@@ -252,16 +263,19 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
     // They wait only for data: a loaded slot, a free output slot.  What they produce for others they hand over with
     // bar.arrive, never waiting for each other.
     const int t = tid & 3;
-    for (int k = 0; k < iters; ++k) {
-        const bool doW = k < Kw;
+    for (int k = 0; k < Kw + FLE_LEAD; ++k) {
         const int kp = k - FLE_LEAD;
-        const long long tileW = c + (long long)k * G, tileP = c + (long long)kp * G;
+        const int sw = k % FLE_WSLOTS;
+        long long tileW = -1;
+        if (k < Kw) {
+            mbar_wait(&w_full[sw], (uint32_t)(k / FLE_WSLOTS) & 1u);
+            tileW = sh.tile[k % FLE_IDS];
+            if (tileW < 0) Kw = k;  // the counter ran out: FLE_LEAD pack touches are left
+        }
 
         // ---- width touch of tile W
-        if (doW) {
-            const int sw = k % FLE_WSLOTS;
+        if (tileW >= 0) {
             const int nfrW = fle_full_frames_of(full_frames, tileW);
-            mbar_wait(&w_full[sw], (uint32_t)(k / FLE_WSLOTS) & 1u);
             const uint8_t* wt = wbuf + sw * FLE_TILE_BYTES;
             // one thread per frame, no shuffles: the eight 16-byte pieces are read in an order rotated by the frame
             // number, so the eight lanes of a quarter-warp hit eight different bank groups (frames are 128 bytes apart)
@@ -288,6 +302,7 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
         if (kp < 0) continue;
 
         // ---- pack touch of tile P
+        const long long tileP = sh.tile[kp % FLE_IDS];
         const int sp = kp % FLE_PSLOTS, so = kp % FLE_OSLOTS, mp = kp % (FLE_LEAD + 1);
         const uint8_t* ptile = pbuf + sp * FLE_TILE_BYTES;
         mbar_wait(&p_full[sp], (uint32_t)(kp / FLE_PSLOTS) & 1u);  // (also: the tile's ring row is complete)
@@ -344,7 +359,7 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
 //                                        launcher
 // =============================================================================================
 static size_t fle_tiles_padded(size_t n) { return (fl_tiles(n) + 255) / 256 * 256; }  // whole scanner chunks
-// workspace: inc[tiles] u64 | agg[tiles] u32
+// workspace: inc[tiles] u64 | agg[tiles] u32 | tile counter
 size_t fl_encode_workspace_bytes(size_t n) { return fle_tiles_padded(n) * 12 + 16; }
 
 cudaError_t fl_encode_launch(const uint8_t* d_in, size_t n, uint8_t* d_bits, uint8_t* d_values, uint64_t* d_values_size,
@@ -353,10 +368,11 @@ cudaError_t fl_encode_launch(const uint8_t* d_in, size_t n, uint8_t* d_bits, uin
     const size_t tiles = fl_tiles(n), tmax = fle_tiles_padded(n);
     uint64_t* inc = reinterpret_cast<uint64_t*>(d_ws);
     uint32_t* agg = reinterpret_cast<uint32_t*>(inc + tmax);
+    unsigned int* next_tile = agg + tmax;
     cudaError_t e = cudaMemsetAsync(d_ws, 0, fl_encode_workspace_bytes(n), stream);
     if (e != cudaSuccess) return e;
     constexpr int smem = (FLE_WSLOTS + FLE_PSLOTS + FLE_OSLOTS) * FLE_TILE_BYTES;
-    // the grid must be fully co-resident: the pack touch waits for the scanner CTA, the scanner for every width touch
+    // persistent CTAs: as many as fit (more would only queue behind them), plus the scanner CTA (block 0, placed first)
     int dev = 0;
     e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
@@ -376,7 +392,7 @@ cudaError_t fl_encode_launch(const uint8_t* d_in, size_t n, uint8_t* d_bits, uin
         if (dev < 64) resident[dev] = cap;
     }
     const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap - 1) + 1;  // the scanner CTA + the workers
-    fl_encode_kernel<<<grid, FLE_THREADS, smem, stream>>>(d_in, n, d_bits, d_values, d_values_size, inc, agg, (long long)tiles);
+    fl_encode_kernel<<<grid, FLE_THREADS, smem, stream>>>(d_in, n, d_bits, d_values, d_values_size, inc, agg, next_tile, (long long)tiles);
     return cudaGetLastError();
 }
 
