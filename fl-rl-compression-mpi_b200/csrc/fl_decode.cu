@@ -12,9 +12,9 @@
 //     brings the widths of 4 tiles, a segmented warp scan gives every frame's offset, and for each
 //     tile one TMA bulk copy of exactly its 16*sum(b) value bytes is issued into a ring of
 //     FLD_STAGES shared-memory stages (full / free mbarriers) — several tiles are always in flight;
-//   * 8 unpack warps wait on the stage's mbarrier, pull their words into registers, release the
-//     stage, unpack lane-locally (flrl_bits.cuh) and store 2 x 16 bytes per lane: a warp writes
-//     1 KiB of contiguous output per item, no staging buffer, no store-side synchronisation.
+//   * 8 unpack warps wait on the stage's mbarrier, pull their words into registers, unpack lane-locally
+//     (flrl_bits.cuh), store 2 x 16 bytes per lane (a warp writes 1 KiB of contiguous output per item, no staging
+//     buffer, no store-side synchronisation) and release the stage.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -27,7 +27,10 @@ namespace flrl {
 
 static constexpr int FLD_TILE_FRAMES = 128;
 static constexpr int FLD_TILE_BYTES = FLD_TILE_FRAMES * 128;  // 16 KiB of output per tile
-static constexpr int FLD_STAGES = 5;
+#ifndef FLD_STAGES_N
+#define FLD_STAGES_N 5
+#endif
+static constexpr int FLD_STAGES = FLD_STAGES_N;
 static constexpr int FLD_UNPACK_THREADS = 256;
 static constexpr int FLD_THREADS = FLD_UNPACK_THREADS + 32;   // + producer warp
 static constexpr int FLD_ITEMS = FLD_TILE_BYTES / 32 / FLD_UNPACK_THREADS;  // 32-byte items per thread per tile = 2
@@ -237,15 +240,6 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
 #pragma unroll
                 for (int j = 0; j < 5; ++j) g[i][j] = w[q + j];
             }
-            {
-                uint32_t x = 0;
-#pragma unroll
-                for (int i = 0; i < FLD_ITEMS; ++i)
-                    x ^= (r[i][0] ^ r[i][1] ^ r[i][2]) ^ (r[i][3] ^ g[i][0] ^ g[i][1]) ^ (g[i][2] ^ g[i][3] ^ g[i][4]);
-                loads_landed(x);
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&freeb[s]);  // everything this warp needs from the stage is in registers
             uint8_t* otile = out + (size_t)(t0 + k) * FLD_TILE_BYTES;
 #pragma unroll
             for (int i = 0; i < FLD_ITEMS; ++i) {
@@ -259,6 +253,10 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
                     o[1] = make_uint4(cc[0], cc[1], cc[2], cc[3]);
                 }
             }
+            // Release the stage only now, after its words were used: an arrive right behind the loads (everything is "in
+            // registers") can overtake them (seen in fl_encode); releasing early measured no faster anyway.
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&freeb[s]);
         }
     }
     // ---- the CTA of the last range: the final partial frame ---------------------------------------

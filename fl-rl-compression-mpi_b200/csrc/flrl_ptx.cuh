@@ -138,14 +138,6 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v)
 }
 
 // named barriers (id 1..15; id 0 is __syncthreads)
-// Keeps what follows behind the shared-memory loads that produced x: the compare cannot issue before x is in its register
-// and issue is in order.  Used before releasing a staged buffer whose contents were only loaded, not yet used: measured
-// in fl_encode, an mbarrier arrive issued right behind the loads let the refill overtake them (wrong bytes about once
-// per 100k tiles).
-__device__ __forceinline__ void loads_landed(uint32_t x)
-{
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %0, 0x9e3779b9;\n\t@p nanosleep.u32 0;\n\t}" ::"r"(x) : "memory");
-}
 __device__ __forceinline__ void bar_sync(uint32_t id, uint32_t nthreads)
 {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
