@@ -48,6 +48,13 @@ static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][
 #ifndef RL_RING_PAIRS
 #define RL_RING_PAIRS 8192
 #endif
+// pause between two looks of a polling loop (ns): the base warp with nothing to hand out / with answers pending
+#ifndef RLE_SLEEP_A
+#define RLE_SLEEP_A 100
+#endif
+#ifndef RLE_SLEEP_B
+#define RLE_SLEEP_B 200
+#endif
 #ifndef RLE_CTAS
 #define RLE_CTAS 6
 #endif
@@ -334,7 +341,7 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             const uint32_t n_meta = ld_volatile_shared(&sh.n_meta);
             if (n_ready == n_meta) {
                 if (done && n_ready == ld_volatile_shared(&sh.n_meta)) break;
-                __nanosleep(100);
+                __nanosleep(RLE_SLEEP_A);
                 continue;
             }
             __threadfence_block();
@@ -363,7 +370,7 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
                     st_volatile_shared(&sh.n_ready, n_ready);
                 }
             } else {
-                __nanosleep(200);
+                __nanosleep(RLE_SLEEP_B);
             }
         }
         return;
@@ -397,7 +404,7 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
         bar_sync(BAR_COMPUTE, RL_THREADS);  // everybody has read the previous snapshot
         if (tid == 0) {
             uint32_t r;
-            while ((r = ld_volatile_shared(&sh.n_ready)) < need) __nanosleep(100);
+            while ((r = ld_volatile_shared(&sh.n_ready)) < need) __nanosleep(RLE_SLEEP_A);
             __threadfence_block();
             sh.store_upto = r;
         }
