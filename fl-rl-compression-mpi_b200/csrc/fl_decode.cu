@@ -27,6 +27,9 @@ namespace flrl {
 
 static constexpr int FLD_TILE_FRAMES = 128;
 static constexpr int FLD_TILE_BYTES = FLD_TILE_FRAMES * 128;  // 16 KiB of output per tile
+#ifndef FLD_EXP
+#define FLD_EXP 0  // timing experiments only: 1 = no unpack arithmetic, 2 = no stores (both: wrong output), 4 = 256-bit stores
+#endif
 #ifndef FLD_STAGES_N
 #define FLD_STAGES_N 5
 #endif
@@ -247,10 +250,23 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
                 if (bw[i]) {
                     const UnpackK kk = make_unpack_k(bw[i]);
                     uint32_t a[4], cc[4];
+#if (FLD_EXP & 1)
+                    (void)kk;
+                    for (int j = 0; j < 4; ++j) a[j] = r[i][j], cc[j] = g[i][j] ^ g[i][4];
+#else
                     unpack32_regs(bw[i], kk, r[i], g[i], a, cc);
+#endif
                     uint4* o = reinterpret_cast<uint4*>(otile + fr * 128 + t * 32);
+#if (FLD_EXP & 2)
+                    if (a[0] == 0x12345679u && cc[3] == 0x9abcdef1u) o[0] = make_uint4(a[0] ^ a[1], a[2] ^ a[3], cc[0] ^ cc[1], cc[2]);
+#elif (FLD_EXP & 4)
+                    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(o), "r"(a[0]), "r"(a[1]), "r"(a[2]),
+                                 "r"(a[3]), "r"(cc[0]), "r"(cc[1]), "r"(cc[2]), "r"(cc[3])
+                                 : "memory");
+#else
                     o[0] = make_uint4(a[0], a[1], a[2], a[3]);
                     o[1] = make_uint4(cc[0], cc[1], cc[2], cc[3]);
+#endif
                 }
             }
             // Release the stage only now, after its words were used: an arrive right behind the loads (everything is "in
