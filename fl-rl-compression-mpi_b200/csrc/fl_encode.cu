@@ -14,16 +14,20 @@
 //   * pack touch of tile t - FLE_LEAD * G, in the same loop iteration (second touch: an L2 hit, evict-first):
 //     (offset, width) from the ring, the tile's offset in `values` (posted thousands of tiles ago: one load, asked
 //     for at the top of the iteration), lane-local multiply/shift packing (flrl_bits.cuh; fl_cpu.cu:64-84; four
-//     lanes per frame) into an output slot, one TMA bulk store (every tile starts on a 16-byte boundary of `values`).
+//     lanes per frame) IN PLACE over the staged tile once every pack warp holds its part in registers, one TMA bulk
+//     store (every tile starts on a 16-byte boundary of `values`).
 // FLE_LEAD * G tiles (~19 MiB) exceed what is in flight and stay inside the 126 MB L2 (a longer lead loses more of
 // the second touches to L2 misses).  The pack warps never wait for each other: everything that joins them — loads,
 // the scan of a tile's widths, the bulk store — goes through the service warp (bar.arrive from the pack warps,
-// bar.sync in the service warp), and the pack warps wait only on mbarriers for data: a loaded slot, a free output slot.
+// bar.sync in the service warp); the pack warps wait on mbarriers for loaded slots and meet once per tile, before the
+// tile is overwritten in place.  Two 16 KiB slots per CTA leave room for 6 CTAs per SM, which is what hides the
+// latencies (a separate output slot, 4 CTAs per SM and no barrier at all: 0.322 ms).
 // The kernel is bound by instruction issue and latency in the pack warps (about 1000 instructions per warp and tile,
 // ~450 of them the packing), not by memory: without the packing arithmetic it runs at 86 % of the HBM bandwidth.
 // (History: one CTA per tile with a look-back, 0.417 ms / GiB; persistent two-touch with widths by shuffles and
 // recomputed in the pack touch, 0.42 ms; widths by one thread per frame + the (offset, width) ring, 0.36 ms; joins
-// moved to the service warp and a lead of 2 iterations, 0.33 ms.)
+// moved to the service warp and a lead of 2 iterations, 0.33 ms; tiles from an atomic counter, 0.32 ms; packing in
+// place and 6 CTAs per SM, 0.307 ms.)
 //
 // Tiles are handed out by an atomic counter (as in the run-length kernels): only running CTAs own tiles, so nothing
 // depends on the whole grid being resident; the launcher still sizes the grid to what fits, plus the scanner CTA.
@@ -47,8 +51,8 @@ static constexpr int FLE_TILE_BYTES = FLE_TILE_FRAMES * 128;  // 16 KiB
 #endif
 static constexpr int FLE_THREADS = FLE_PACK + 32;             // + service warp
 static constexpr int FLE_ITEMS = 4 * FLE_TILE_FRAMES / FLE_PACK;  // 32-byte items per thread per tile
-// 16 KiB slots per CTA: width touch, pack touch, packed output.  One of each and 4 CTAs / SM measured best
-// (more slots with 3 CTAs / SM: 0.44 ms; 256 pack threads: 0.46 ms).
+// 16 KiB slots per CTA: width touch, pack touch (packed in place), and with !FLE_INPLACE a separate output slot.
+// One of each measured best (more slots and fewer CTAs / SM: slower every time; 256 pack threads: slower).
 #ifndef FLE_WSLOTS
 #define FLE_WSLOTS 1
 #endif
@@ -58,8 +62,11 @@ static constexpr int FLE_ITEMS = 4 * FLE_TILE_FRAMES / FLE_PACK;  // 32-byte ite
 #ifndef FLE_OSLOTS
 #define FLE_OSLOTS 1
 #endif
+#ifndef FLE_INPLACE
+#define FLE_INPLACE 1  // 1: pack in place over the staged tile (no output slot; one barrier of the pack warps per tile)
+#endif
 #ifndef FLE_CTAS
-#define FLE_CTAS 4  // per SM
+#define FLE_CTAS 6  // per SM
 #endif
 #ifndef FLE_LEAD
 #define FLE_LEAD 2  // iterations between the two touches of a tile (1: 0.370 ms, 2: 0.328, 3: 0.337, 5: 0.356)
@@ -122,9 +129,9 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* const wbuf = smem;                                 // FLE_WSLOTS x 16 KiB: width touch
     uint8_t* const pbuf = smem + FLE_WSLOTS * FLE_TILE_BYTES;   // FLE_PSLOTS x 16 KiB: pack touch
-    uint8_t* const obuf = pbuf + FLE_PSLOTS * FLE_TILE_BYTES;   // FLE_OSLOTS x 16 KiB: the packed tile, source of the bulk store
+    [[maybe_unused]] uint8_t* const obuf = pbuf + FLE_PSLOTS * FLE_TILE_BYTES;  // !FLE_INPLACE: FLE_OSLOTS x 16 KiB, the packed tile
     __shared__ __align__(8) uint64_t w_full[FLE_WSLOTS], w_free[FLE_WSLOTS], p_full[FLE_PSLOTS], p_free[FLE_PSLOTS],
-        o_free[FLE_OSLOTS];
+        o_free[FLE_OSLOTS > 0 ? FLE_OSLOTS : 1];
     __shared__ FleShared sh;
     __shared__ __align__(16) uint4 ktab[9];  // PackK{k1,k2,k3,ra} per width
     __shared__ uint32_t tail_scratch[36];
@@ -148,7 +155,7 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
             mbar_init(&p_full[s], 1);
             mbar_init(&p_free[s], FLE_PACK / 32);
         }
-        for (int s = 0; s < FLE_OSLOTS; ++s) mbar_init(&o_free[s], 1);
+        for (int s = 0; s < (FLE_OSLOTS > 0 ? FLE_OSLOTS : 1); ++s) mbar_init(&o_free[s], 1);
         fence_mbar_init();
     }
     if (tid <= 8) {
@@ -193,7 +200,9 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
             uint64_t g = 1ull << 63;
             if (doP) {  // second touch: an L2 hit, not needed afterwards
                 const int sp = kp % FLE_PSLOTS;
+#if !FLE_INPLACE
                 if (kp >= FLE_PSLOTS) mbar_wait(&p_free[sp], (uint32_t)(kp / FLE_PSLOTS - 1) & 1u);
+#endif  // (in place: this warp waited for the slot's last bulk store itself, right after issuing it)
                 if (lane == 0) {
                     const uint32_t nfr = (uint32_t)fle_full_frames_of(full_frames, tileP);
                     if (nfr) {
@@ -239,7 +248,13 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
                 load_w(k + 1);  // its slot was released before the pack warps arrived at the barrier above
             }
             if (doP) {
-                const int so = kp % FLE_OSLOTS, mp = kp % (FLE_LEAD + 1);
+#if FLE_INPLACE
+                const int so = kp % FLE_PSLOTS;
+                uint8_t* const obuf = pbuf;
+#else
+                const int so = kp % FLE_OSLOTS;
+#endif
+                const int mp = kp % (FLE_LEAD + 1);
                 bar_sync(BAR_O, FLE_THREADS);  // tile P is packed (and fenced for the bulk store)
                 if (lane == 0) {
                     while ((g >> 63) == 0) {
@@ -250,8 +265,10 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
                     const uint32_t total = sh.total[mp];
                     if (total) tma_store_1d_hint(values + base * 16, obuf + so * FLE_TILE_BYTES, total * 16, drop);
                     tma_store_commit();
-                    tma_store_wait_read<0>();
+                    tma_store_wait_read<0>();  // (in place: the slot may be loaded again — this warp does that itself)
+#if !FLE_INPLACE
                     mbar_arrive(&o_free[so]);  // the output slot may be written again
+#endif
                 }
                 __syncwarp();
             }
@@ -303,7 +320,7 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
 
         // ---- pack touch of tile P
         const long long tileP = sh.tile[kp % FLE_IDS];
-        const int sp = kp % FLE_PSLOTS, so = kp % FLE_OSLOTS, mp = kp % (FLE_LEAD + 1);
+        const int sp = kp % FLE_PSLOTS, mp = kp % (FLE_LEAD + 1);
         const uint8_t* ptile = pbuf + sp * FLE_TILE_BYTES;
         mbar_wait(&p_full[sp], (uint32_t)(kp / FLE_PSLOTS) & 1u);  // (also: the tile's ring row is complete)
         uint4 A[FLE_ITEMS], C[FLE_ITEMS];
@@ -316,9 +333,16 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
             C[i] = p[1];
             M[i] = sh.meta[mp][fr];  // (offset in 16-byte units) << 8 | width
         }
+#if FLE_INPLACE
+        bar_sync(BAR_P, FLE_PACK);  // every pack warp has the tile in registers: it is overwritten with the packed words
+        {
+            const uint32_t tw = smem_u32(ptile);
+#else
+        const int so = kp % FLE_OSLOTS;
         if (kp >= FLE_OSLOTS) mbar_wait(&o_free[so], (uint32_t)(kp / FLE_OSLOTS - 1) & 1u);  // its last bulk store has read it
         {
             const uint32_t tw = smem_u32(obuf + so * FLE_TILE_BYTES);
+#endif
 #pragma unroll
             for (int i = 0; i < FLE_ITEMS; ++i) {
                 const uint32_t b = M[i] & 0xffu;  // 0 for frames past the end: every store below is predicated off
@@ -337,8 +361,10 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
         }
         // every shared-memory read of the staged tile has returned (its values were used above): the slot may be refilled.
         // (Not earlier: an arrive right behind the loads can overtake them.)
+#if !FLE_INPLACE
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_free[sp]);
+#endif
         fence_proxy_async_smem();          // the packed tile is read by a bulk store
         bar_arrive(BAR_O, FLE_THREADS);    // over to the service warp, which stores it
 
@@ -371,7 +397,7 @@ cudaError_t fl_encode_launch(const uint8_t* d_in, size_t n, uint8_t* d_bits, uin
     unsigned int* next_tile = agg + tmax;
     cudaError_t e = cudaMemsetAsync(d_ws, 0, fl_encode_workspace_bytes(n), stream);
     if (e != cudaSuccess) return e;
-    constexpr int smem = (FLE_WSLOTS + FLE_PSLOTS + FLE_OSLOTS) * FLE_TILE_BYTES;
+    constexpr int smem = (FLE_WSLOTS + FLE_PSLOTS + (FLE_INPLACE ? 0 : FLE_OSLOTS)) * FLE_TILE_BYTES;
     // persistent CTAs: as many as fit (more would only queue behind them), plus the scanner CTA (block 0, placed first)
     int dev = 0;
     e = cudaGetDevice(&dev);
