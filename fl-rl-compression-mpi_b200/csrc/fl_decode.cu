@@ -38,7 +38,10 @@ static constexpr int FLD_UNPACK_THREADS = 256;
 static constexpr int FLD_THREADS = FLD_UNPACK_THREADS + 32;   // + producer warp
 static constexpr int FLD_ITEMS = FLD_TILE_BYTES / 32 / FLD_UNPACK_THREADS;  // 32-byte items per thread per tile = 2
 static constexpr int FLD_STAGE_BYTES = FLD_TILE_BYTES + 128;  // slack for the unpacker's over-reads
-static constexpr int FLD_CTAS_PER_SM = 2;
+#ifndef FLD_CTAS
+#define FLD_CTAS 2
+#endif
+static constexpr int FLD_CTAS_PER_SM = FLD_CTAS;
 
 struct __align__(16) FldMeta {
     uint16_t off[FLD_TILE_FRAMES];  // exclusive prefix of widths inside the tile (16-byte units)
