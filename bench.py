@@ -386,9 +386,9 @@ def run_ours(args):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) from the committed `ncu --set full` captures
-# (profiles/r01_run7_*_ncu_full.csv; 1 GiB per launch, the bench's default size)
+# (profiles/r01_run8_fl_ncu_full.csv for FL, r01_run7_*_ncu_full.csv for RL; 1 GiB per launch, the bench's default size)
 TRAFFIC = {
-    ("fl", "fl_encode_kernel"): 1_635_879_000, ("fl", "fl_decode_kernel"): 1_640_875_000,
+    ("fl", "fl_encode_kernel"): 1_643_363_000, ("fl", "fl_decode_kernel"): 1_640_467_000,
     ("rl4", "rl_encode_kernel"): 1_578_695_000, ("rl4", "rl_decode_kernel"): 1_558_388_000,
     ("rl64", "rl_encode_kernel"): 1_110_706_000, ("rl64", "rl_decode_kernel"): 1_054_236_000,
     ("rl4096", "rl_encode_kernel"): 1_087_804_000, ("rl4096", "rl_decode_kernel"): 1_030_106_000,
