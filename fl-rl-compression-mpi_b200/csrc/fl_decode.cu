@@ -34,7 +34,10 @@ static constexpr int FLD_TILE_BYTES = FLD_TILE_FRAMES * 128;  // 16 KiB of outpu
 #define FLD_STAGES_N 5
 #endif
 static constexpr int FLD_STAGES = FLD_STAGES_N;
-static constexpr int FLD_UNPACK_THREADS = 256;
+#ifndef FLD_UNPACK
+#define FLD_UNPACK 256
+#endif
+static constexpr int FLD_UNPACK_THREADS = FLD_UNPACK;
 static constexpr int FLD_THREADS = FLD_UNPACK_THREADS + 32;   // + producer warp
 static constexpr int FLD_ITEMS = FLD_TILE_BYTES / 32 / FLD_UNPACK_THREADS;  // 32-byte items per thread per tile = 2
 static constexpr int FLD_STAGE_BYTES = FLD_TILE_BYTES + 128;  // slack for the unpacker's over-reads

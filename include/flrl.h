@@ -55,7 +55,9 @@ int flrl_version(void);
 
 /* ceil(n / 128): number of frames == bytes of the widths array (fl_cpu.cu:21). */
 size_t flrl_fl_frames(size_t n);
-/* Scratch for one encode or decode call over n uncompressed bytes (look-back descriptors). */
+/* Scratch for one encode or decode call over n uncompressed bytes (per 16 KiB tile: the scanner's 12 bytes for the
+ * encoder, a look-back descriptor for the decoder).  One workspace per call in flight: calls that overlap on different
+ * streams need their own. */
 size_t flrl_fl_workspace_bytes(size_t n);
 
 /*
