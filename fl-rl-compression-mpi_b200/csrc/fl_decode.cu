@@ -28,7 +28,8 @@ namespace flrl {
 static constexpr int FLD_TILE_FRAMES = 128;
 static constexpr int FLD_TILE_BYTES = FLD_TILE_FRAMES * 128;  // 16 KiB of output per tile
 #ifndef FLD_EXP
-#define FLD_EXP 0  // timing experiments only: 1 = no unpack arithmetic, 2 = no stores (both: wrong output), 4 = 256-bit stores
+#define FLD_EXP 0  // timing experiments only: 1 = no unpack arithmetic, 2 = no stores (both: wrong output), 4 = 256-bit stores,
+                   // 8 = streaming stores (st.cs), 16 = write-through stores (st.wt): none of 1, 4, 8, 16 changes the time
 #endif
 #ifndef FLD_STAGES_N
 #define FLD_STAGES_N 5
@@ -269,6 +270,12 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
                     asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(o), "r"(a[0]), "r"(a[1]), "r"(a[2]),
                                  "r"(a[3]), "r"(cc[0]), "r"(cc[1]), "r"(cc[2]), "r"(cc[3])
                                  : "memory");
+#elif (FLD_EXP & 8)
+                    __stcs(o, make_uint4(a[0], a[1], a[2], a[3]));
+                    __stcs(o + 1, make_uint4(cc[0], cc[1], cc[2], cc[3]));
+#elif (FLD_EXP & 16)
+                    __stwt(o, make_uint4(a[0], a[1], a[2], a[3]));
+                    __stwt(o + 1, make_uint4(cc[0], cc[1], cc[2], cc[3]));
 #else
                     o[0] = make_uint4(a[0], a[1], a[2], a[3]);
                     o[1] = make_uint4(cc[0], cc[1], cc[2], cc[3]);
