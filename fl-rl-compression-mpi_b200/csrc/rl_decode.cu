@@ -3,7 +3,7 @@
 // The reference documents RL decode as "prescan of the counts + binary search" (IMPLEMENTATION-PLAN.md:154-179)
 // and ships no code.  Structure here:
 //
-//   * persistent CTAs (grid = what fits on the device) take 4096-pair tiles from an atomic counter;
+//   * persistent CTAs (grid = what fits on the device) take tiles of 4096 pairs (fewer when that would leave a CTA with too few tiles) from an atomic counter;
 //   * a service warp per CTA runs AHEAD of the compute warps through a ring of tile slots: tile id, TMA bulk
 //     loads of the tile's counts and values, sum of the counts (= the tile's output bytes; a count of 0 is
 //     malformed and flagged) posted to the grid's scanner warp (rl_scan.cuh), which answers with the tile's first
@@ -56,7 +56,7 @@ struct RldSlotMeta {
 __global__ void __launch_bounds__(RLD_ALL, RLD_CTAS_PER_SM)
 rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__ values, size_t pairs, uint8_t* __restrict__ out,
                  size_t out_cap, uint64_t* __restrict__ d_out_size, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg,
-                 uint32_t* __restrict__ next_tile, int* __restrict__ err, long long tiles)
+                 uint32_t* __restrict__ next_tile, int* __restrict__ err, long long tiles, uint32_t tile_pairs)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* const slots = smem;                                                      // RLD_SLOTS x [counts 4096][values 4096]
@@ -98,8 +98,8 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
                 }
                 break;
             }
-            const size_t p0 = (size_t)tile * RLD_PAIRS;
-            const uint32_t np = (uint32_t)(pairs - p0 < (size_t)RLD_PAIRS ? pairs - p0 : RLD_PAIRS);
+            const size_t p0 = (size_t)tile * tile_pairs;  // tile_pairs <= RLD_PAIRS, a multiple of 16
+            const uint32_t np = (uint32_t)(pairs - p0 < (size_t)tile_pairs ? pairs - p0 : tile_pairs);
             const uint32_t np16 = np & ~15u;
             uint8_t* cnt = slots + s * 2 * RLD_PAIRS;
             uint8_t* val = cnt + RLD_PAIRS;
@@ -285,7 +285,17 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
 // =============================================================================================
 //                                        launchers
 // =============================================================================================
-size_t rl_decode_tiles(size_t pairs) { return ((pairs + RLD_PAIRS - 1) / RLD_PAIRS + 255) / 256 * 256; }  // padded: whole scanner chunks
+// A tile is 4096 pairs unless that leaves the persistent CTAs with fewer than ~6 tiles each (long runs: a tile of 4096
+// pairs is up to 1 MiB of output, and 1024 such tiles over 591 CTAs end 14 % late): then 2048 or 1024.
+static constexpr int RLD_MIN_PAIRS = 1024;
+static uint32_t rl_decode_tile_pairs(size_t pairs, size_t workers)
+{
+    uint32_t tp = RLD_PAIRS;
+    while (tp > RLD_MIN_PAIRS && pairs / tp < 6 * workers) tp /= 2;
+    return tp;
+}
+// sized for the smallest tile, padded to whole scanner chunks
+size_t rl_decode_tiles(size_t pairs) { return ((pairs + RLD_MIN_PAIRS - 1) / RLD_MIN_PAIRS + 255) / 256 * 256; }
 // workspace: inc[tiles] u64 | agg[tiles] u32 | tile counter u32 | status int
 size_t rl_decode_workspace_bytes(size_t pairs) { return rl_decode_tiles(pairs) * 12 + 16; }
 const int* rl_decode_status(const void* d_ws, size_t pairs)
@@ -296,7 +306,7 @@ const int* rl_decode_status(const void* d_ws, size_t pairs)
 cudaError_t rl_decode_launch(const uint8_t* d_counts, const uint8_t* d_values, size_t pairs, uint8_t* d_out, size_t out_cap,
                              uint64_t* d_out_size, void* d_ws, cudaStream_t stream)
 {
-    const size_t tiles = (pairs + RLD_PAIRS - 1) / RLD_PAIRS, tmax = rl_decode_tiles(pairs);
+    const size_t tmax = rl_decode_tiles(pairs);
     uint64_t* inc = reinterpret_cast<uint64_t*>(d_ws);
     uint32_t* agg = reinterpret_cast<uint32_t*>(inc + tmax);
     uint32_t* next_tile = agg + tmax;
@@ -323,9 +333,11 @@ cudaError_t rl_decode_launch(const uint8_t* d_counts, const uint8_t* d_values, s
         if (cap < 2) return cudaErrorLaunchOutOfResources;
         if (dev < 64) resident[dev] = cap;
     }
+    const uint32_t tp = rl_decode_tile_pairs(pairs, (size_t)cap - 1);
+    const size_t tiles = (pairs + tp - 1) / tp;
     const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap - 1) + 1;  // the scanner CTA + the workers
     rl_decode_kernel<<<grid, RLD_ALL, smem, stream>>>(d_counts, d_values, pairs, d_out, out_cap, d_out_size, inc, agg, next_tile, err,
-                                                      (long long)tiles);
+                                                      (long long)tiles, tp);
     return cudaGetLastError();
 }
 
