@@ -391,7 +391,7 @@ TRAFFIC = {
     ("fl", "fl_encode_kernel"): 1_643_363_000, ("fl", "fl_decode_kernel"): 1_640_467_000,
     ("rl4", "rl_encode_kernel"): 1_578_695_000, ("rl4", "rl_decode_kernel"): 1_558_388_000,
     ("rl64", "rl_encode_kernel"): 1_110_706_000, ("rl64", "rl_decode_kernel"): 1_054_236_000,
-    ("rl4096", "rl_encode_kernel"): 1_087_804_000, ("rl4096", "rl_decode_kernel"): 1_030_106_000,
+    ("rl4096", "rl_encode_kernel"): 1_087_804_000, ("rl4096", "rl_decode_kernel"): 1_028_774_000,
 }
 
 
