@@ -41,7 +41,10 @@ static constexpr int RL_THREADS = RL_WARPS * 32;        // compute threads
 static constexpr int RLE_THREADS = RL_THREADS + 64;     // + service warp + base warp
 static constexpr int RL_SEG = 32;                       // input bytes per thread per sub-tile
 static constexpr int RL_SUB = RL_THREADS * RL_SEG;      // 4 KiB
-static constexpr int RL_NSUB = 4;
+#ifndef RL_NSUB_N
+#define RL_NSUB_N 4
+#endif
+static constexpr int RL_NSUB = RL_NSUB_N;               // 4 KiB sub-tiles per tile
 static constexpr int RL_TILE = RL_SUB * RL_NSUB;        // 16 KiB
 static constexpr int RL_NCHUNK = RL_NSUB * RL_WARPS;    // warp chunks (1 KiB) per tile
 static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][pad]
