@@ -57,6 +57,11 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gsrc, ui
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// global -> L2 only (no destination, no completion to wait for): bytes a multiple of 16, 16-byte aligned address
+__device__ __forceinline__ void tma_prefetch_l2(const void* gsrc, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
 // shared -> global bulk copy (bulk async-group completion)
 __device__ __forceinline__ void tma_store_1d(void* gdst, const void* smem_src, uint32_t bytes)
 {

@@ -58,6 +58,9 @@ static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][
 #ifndef RLE_SLEEP_B
 #define RLE_SLEEP_B 200
 #endif
+#ifndef RLE_PF_LEAD
+#define RLE_PF_LEAD 1024  // tiles between a load and the L2 prefetch issued with it (0: none)
+#endif
 #ifndef RLE_CTAS
 #define RLE_CTAS 6
 #endif
@@ -279,6 +282,15 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
                     } else {
                         mbar_arrive(&full[lane]);
                     }
+#if RLE_PF_LEAD
+                    // A CTA has one input buffer, so a tile pays its load latency in full: make that an L2 hit.  Whoever
+                    // loads tile t asks L2 for tile t + RLE_PF_LEAD (somebody else's, about one grid of tiles later).
+                    {
+                        const size_t pb = tbase + (size_t)RLE_PF_LEAD * RL_TILE + (size_t)lane * RL_SUB;
+                        const size_t pe = dmin(pb + RL_SUB, n_avail & ~(size_t)15);
+                        if (pe > pb) tma_prefetch_l2(in + pb, (uint32_t)(pe - pb));
+                    }
+#endif
                 }
             }
             TRACE(0);
