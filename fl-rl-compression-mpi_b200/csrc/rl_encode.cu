@@ -3,19 +3,28 @@
 // The reference documents RL (IMPLEMENTATION-PLAN.md:83-152: mask -> scan -> start indices -> split of
 // runs > 255 -> emit) but ships no code.  Structure here:
 //
-//   * small persistent CTAs (6 per SM) that take 16 KiB tiles from an atomic counter, so tile order is time
-//     order: everything a tile depends on was started earlier, by a CTA that never waits for a later tile;
-//   * 4 compute warps, thread = one 32-byte segment per 4 KiB sub-tile (four TMA bulk loads per tile, each with
-//     its own mbarrier): run-start bit mask (XOR with the byte-shifted word, SWAR non-zero-byte test, IDP.4A
-//     gathers the byte flags into mask bits) -> nearest earlier run start S by ballot (no shuffle scan) -> the
-//     one possible 255-split of the segment, (i - S) % 255 == 0 (the plan's ":125" rule, replacing its iterative
-//     rescan loop; skipped when the entering run is too short to reach 255) -> warp sum-scans of the pair
-//     counts -> compaction of values and LAGGED counts (a pair's count is written when the NEXT boundary is
-//     found: no look-ahead halo, no suffix scan) into a shared-memory RING of staged pairs;
+//   * persistent CTAs (4 per SM) take 16 KiB tiles from an atomic counter, so tile order is time order:
+//     everything a tile depends on was started earlier, by a CTA that never waits for a later tile.  The CTA
+//     that runs first becomes the grid's scanner (role counter), so nothing depends on CTA placement or on
+//     the whole grid being resident;
+//   * a tile is 128 ROWS of 128 bytes, loaded by TMA as a 2-D tensor with the 128-byte swizzle (four boxes of
+//     32 rows, one mbarrier each, two tile buffers per CTA so the next tile lands while this one is worked on):
+//     a thread owns one row and reads it with eight conflict-free LDS.128 (16-byte piece j of row r sits at
+//     piece j ^ (r & 7)); a warp owns 4 KiB of consecutive bytes;
+//   * per row: run-start bit mask of its 128 bytes (XOR with the byte-shifted word, SWAR non-zero-byte test,
+//     IDP.4A gathers the byte flags into mask bits) -> nearest earlier run start S inside the warp by ballot ->
+//     the one possible 255-split of the row, (i - S) % 255 == 0 (the plan's ":125" rule, replacing its
+//     iterative rescan loop) -> ONE warp scan of the pair counts.  The leading rows of a warp (no run start
+//     before them inside the warp) get their splits in closed form once the previous warps' last run starts
+//     are known (one named barrier per tile); the leading part of the TILE gets them from the service warp's
+//     look-back, also in closed form;
+//   * compaction into a shared-memory RING of staged pairs: the value and the POSITION (mod 256) of every pair
+//     boundary.  A pair's count is the difference of two neighbouring positions (boundaries are never more
+//     than 255 apart), taken when the tile is written: no look-ahead halo, no suffix scan, no per-pair count
+//     arithmetic in the divergent loop;
 //   * the compute warps never wait for another CTA: a tile's pairs stay in the ring until its first slot is
-//     known and are written then, several tiles later (measured: the first slot arrives ~7 us after the
-//     tile's pair count is posted, because it needs the slowest of some hundred earlier tiles); 16-byte
-//     stores aligned in the GLOBAL address space (unaligned shared reads fixed up with PRMT);
+//     known and are written then, a few tiles later; 16-byte stores aligned in the GLOBAL address space
+//     (unaligned shared reads fixed up with PRMT);
 //   * a service warp per CTA: tile ids, loads, look-back #1 (start of the run that enters the tile: gives the
 //     splits that fall before the tile's first run start and the count of the PREVIOUS tile's last pair,
 //     which this tile writes), posts the tile's pair count;
@@ -24,7 +33,9 @@
 //     the slots of the CTA's waiting tiles, one lane per tile.
 //
 // A pair belongs to the tile (and the shard) in which it STARTS; its count looks ahead up to 255 bytes, so
-// tiles and shards concatenate to the single-stream output byte for byte.
+// tiles and shards concatenate to the single-stream output byte for byte.  tools/model_rle.py is the same
+// arithmetic on the CPU, checked against the oracle.
+#include <cuda.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -37,17 +48,12 @@
 namespace flrl {
 
 static constexpr int RL_WARPS = 4;                      // compute warps
-static constexpr int RL_THREADS = RL_WARPS * 32;        // compute threads
+static constexpr int RL_THREADS = RL_WARPS * 32;        // compute threads = rows per tile
 static constexpr int RLE_THREADS = RL_THREADS + 64;     // + service warp + base warp
-static constexpr int RL_SEG = 32;                       // input bytes per thread per sub-tile
-static constexpr int RL_SUB = RL_THREADS * RL_SEG;      // 4 KiB
-#ifndef RL_NSUB_N
-#define RL_NSUB_N 4
-#endif
-static constexpr int RL_NSUB = RL_NSUB_N;               // 4 KiB sub-tiles per tile
-static constexpr int RL_TILE = RL_SUB * RL_NSUB;        // 16 KiB
-static constexpr int RL_NCHUNK = RL_NSUB * RL_WARPS;    // warp chunks (1 KiB) per tile
-static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][pad]
+static constexpr int RL_ROW = 128;                      // bytes per thread and tile (the swizzle span)
+static constexpr int RL_TILE = RL_ROW * RL_THREADS;     // 16 KiB
+static constexpr int RL_WSPAN = RL_TILE / RL_WARPS;     // 4 KiB of consecutive bytes per warp = one TMA box of 32 rows
+static constexpr int RL_NBUF = 2;                       // tile buffers per CTA
 #ifndef RL_RING_PAIRS
 #define RL_RING_PAIRS 8192
 #endif
@@ -62,16 +68,17 @@ static constexpr int RL_INBUF = 16 + RL_TILE + 16;      // [16 left halo][tile][
 #define RLE_PF_LEAD 1024  // tiles between a load and the L2 prefetch issued with it (0: none)
 #endif
 #ifndef RLE_CTAS
-#define RLE_CTAS 6
+#define RLE_CTAS 4
 #endif
 static constexpr int RL_RING = RL_RING_PAIRS;           // staged pairs (power of two)
-static constexpr int RL_RINGB = RL_RING + 32;           // + over-read slack of the unaligned 16-byte reads
+static constexpr int RL_RINGB = RL_RING + 32;           // + mirror of entry 0 + over-read slack of the unaligned 16-byte reads
 static constexpr int RLE_Q = 32;                        // tiles of one CTA that may wait for their first slot
 static constexpr int RLE_CTAS_PER_SM = RLE_CTAS;
 static constexpr uint64_t RL_BIAS = 255;                // run starts are stored as S + 255 >= 0
 static constexpr uint32_t BAR_COMPUTE = 1;              // named barrier of the compute warps
-static_assert(RL_NCHUNK <= 32 && RL_NSUB % 2 == 0, "chunk arrays are handled by one warp; sub-tiles are scanned in pairs");
-static_assert((RL_RING & (RL_RING - 1)) == 0 && RL_RING <= RL_TILE, "ring indices are masked");
+static constexpr int RLE_SMEM = 1024 + RL_NBUF * RL_TILE + 2 * RL_RINGB;  // 1 KiB: the swizzle needs 1024-byte aligned buffers
+static_assert((RL_RING & (RL_RING - 1)) == 0 && RL_RING >= 512, "ring indices are masked");
+static_assert(RL_ROW == 128 && RL_WSPAN == 32 * RL_ROW, "one row per lane, one 32-row box per warp");
 
 // ---- run-start flags of 32 consecutive bytes -------------------------------------------------
 // bit (4k + j) of the result: byte j of word k differs from the byte before it.
@@ -92,13 +99,6 @@ __device__ __forceinline__ uint32_t start_mask32(const uint32_t (&w)[8], uint32_
         prev = w[k + 1];
     }
     return (v[0] >> 7) + v[1] * 2u + v[2] * 512u + v[3] * 131072u;
-}
-__device__ __forceinline__ uint32_t segment_mask(const uint8_t* inbuf, int off)
-{
-    const uint4 a = *reinterpret_cast<const uint4*>(inbuf + 16 + off);
-    const uint4 b = *reinterpret_cast<const uint4*>(inbuf + 32 + off);
-    const uint32_t w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-    return start_mask32(w, *reinterpret_cast<const uint32_t*>(inbuf + 12 + off));
 }
 
 // look-back #1: biased start of the last run that begins before tile `tile`.
@@ -129,10 +129,21 @@ __device__ __forceinline__ uint4 lds_unaligned16(const uint8_t* buf, uint32_t u)
     const uint32_t a = w[0], b = w[1], c = w[2], d = w[3], e = w[4];
     return make_uint4(__byte_perm(a, b, sel), __byte_perm(b, c, sel), __byte_perm(c, d, sel), __byte_perm(d, e, sel));
 }
+// 16 counts from 17 staged positions: pos[u + i + 1] - pos[u + i] (mod 256), i = 0 .. 15
+__device__ __forceinline__ uint4 lds_diff16(const uint8_t* buf, uint32_t u)
+{
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(buf) + (u >> 2);
+    const uint32_t s0 = 0x3210u + 0x1111u * (u & 3u), s1 = s0 + 0x1111u;  // shift 4 selects the whole next word
+    const uint32_t a = w[0], b = w[1], c = w[2], d = w[3], e = w[4];
+    return make_uint4(__vsub4(__byte_perm(a, b, s1), __byte_perm(a, b, s0)), __vsub4(__byte_perm(b, c, s1), __byte_perm(b, c, s0)),
+                      __vsub4(__byte_perm(c, d, s1), __byte_perm(c, d, s0)), __vsub4(__byte_perm(d, e, s1), __byte_perm(d, e, s0)));
+}
 
-// cnt staged bytes stage[soff .. soff + cnt) -> dst[g0 .. g0 + cnt): coalesced 16-byte stores on 16-byte aligned
+// cnt output bytes derived from stage[soff ..] -> dst[g0 .. g0 + cnt): coalesced 16-byte stores on 16-byte aligned
 // global addresses, the (at most 15 + 15) bytes of the two ragged ends as one byte store per thread; nothing at
-// or past index `cap` is written.
+// or past index `cap` is written.  DIFF: the output byte i is stage[soff + i + 1] - stage[soff + i] (a count from
+// two positions), else stage[soff + i] (a value).
+template <bool DIFF>
 __device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint64_t g0, uint32_t cnt, uint64_t cap,
                                                 const uint8_t* stage, uint32_t soff, int tid)
 {
@@ -143,19 +154,22 @@ __device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint6
     const uint32_t nfull = (cnt - head) >> 4;               // aligned 16-byte chunks
     const uint32_t tail0 = head + 16u * nfull;              // staging index of the first byte after them
     for (uint32_t q = tid; q < nfull; q += RL_THREADS)
-        *reinterpret_cast<uint4*>(dst + g0 + head + 16u * q) = lds_unaligned16(stage, soff + head + 16u * q);
-    if ((uint32_t)tid < head) dst[g0 + tid] = stage[soff + tid];
+        *reinterpret_cast<uint4*>(dst + g0 + head + 16u * q) =
+            DIFF ? lds_diff16(stage, soff + head + 16u * q) : lds_unaligned16(stage, soff + head + 16u * q);
+    if ((uint32_t)tid < head) dst[g0 + tid] = DIFF ? (uint8_t)(stage[soff + tid + 1] - stage[soff + tid]) : stage[soff + tid];
     const uint32_t t2 = (uint32_t)tid - 16u;                // threads 16..31 take the tail
-    if (t2 < cnt - tail0) dst[g0 + tail0 + t2] = stage[soff + tail0 + t2];
+    if (t2 < cnt - tail0)
+        dst[g0 + tail0 + t2] = DIFF ? (uint8_t)(stage[soff + tail0 + t2 + 1] - stage[soff + tail0 + t2]) : stage[soff + tail0 + t2];
 }
-// the same from a ring of RL_RING bytes: at most two linear pieces
+// the same from a ring of RL_RING bytes: at most two linear pieces (entry RL_RING mirrors entry 0 for the differences)
+template <bool DIFF>
 __device__ __forceinline__ void store_from_ring(uint8_t* __restrict__ dst, uint64_t g0, uint32_t cnt, uint64_t cap,
                                                 const uint8_t* ring, uint32_t head, int tid)
 {
     const uint32_t h = head & (RL_RING - 1);
     const uint32_t first = min(cnt, (uint32_t)RL_RING - h);
-    store_compacted(dst, g0, first, cap, ring, h, tid);
-    if (cnt > first) store_compacted(dst, g0 + first, cnt - first, cap, ring, 0, tid);
+    store_compacted<DIFF>(dst, g0, first, cap, ring, h, tid);
+    if (cnt > first) store_compacted<DIFF>(dst, g0 + first, cnt - first, cap, ring, 0, tid);
 }
 
 template <typename T>
@@ -163,28 +177,26 @@ __device__ __forceinline__ T dmin(T a, T b) { return a < b ? a : b; }
 template <typename T>
 __device__ __forceinline__ T dmax(T a, T b) { return a > b ? a : b; }
 
-#ifdef FLRL_TRACE
-// development aid (variant builds only): per-tile globaltimer stamps
-__device__ uint64_t* g_rle_trace = nullptr;
-__device__ __forceinline__ uint64_t gtime()
+// 2-D tensor load of one box (128 bytes x 32 rows, 128-byte swizzle) starting at row `row`
+__device__ __forceinline__ void tma_load_rows(void* smem_dst, const CUtensorMap* tmap, int row, uint64_t* bar)
 {
-    uint64_t t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(reinterpret_cast<uint64_t>(tmap)), "r"(0), "r"(row), "r"(smem_u32(bar))
+                 : "memory");
 }
-#define TRACE(slot)                                                                      \
-    do {                                                                                 \
-        if (g_rle_trace && lane == 0) g_rle_trace[(size_t)tile * 16 + (slot)] = gtime(); \
-    } while (0)
-#else
-#define TRACE(slot) do { } while (0)
-#endif
+__device__ __forceinline__ void mbar_expect_tx_only(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// byte i of row r of a swizzled tile buffer
+__device__ __forceinline__ uint32_t swz(uint32_t r, uint32_t i) { return r * RL_ROW + ((((i >> 4) ^ r) & 7u) << 4) + (i & 15u); }
 
 struct RlePending {               // a tile of this CTA, from "taken" to "stored"
     // written by the compute warps
     uint32_t head;                 // ring position of the tile's first staged pair
-    uint32_t total;                // staged pairs that wait in the ring
-    uint32_t total_all;            // pair boundaries of the tile after its first run start (emitted or not)
+    uint32_t total;                // staged pairs that are emitted (start before n)
+    uint32_t total_all;            // staged pair boundaries (after the tile's first run start), emitted or not
     uint32_t first_byte;           // in[tile base]: the value of the run that enters the tile
     // written by the service warp
     long long tile;
@@ -198,16 +210,26 @@ struct RlePending {               // a tile of this CTA, from "taken" to "stored
     uint64_t g0;                   // first pair slot of the tile
 };
 
+struct RleMeta {                   // compute warps -> service warp, per tile
+    int first_start;               // first run start of the tile (tile relative), RL_TILE if none
+    int last_start;                // last run start, -1 if none
+    uint32_t total_all;            // staged boundaries
+    uint32_t total_emit;           // those before n
+};
+
 struct RleShared {
-    int chunk_first[RL_NCHUNK];    // first run start in each 1 KiB warp chunk (tile relative), RL_TILE if none
-    int chunk_last[RL_NCHUNK];     // last run start in each warp chunk (tile relative), -1 if none
-    uint32_t chunk_cnt[RL_NCHUNK]; // pair boundaries in each warp chunk
-    uint32_t emit_cnt[RL_WARPS];   // ragged tiles only: boundaries at positions < n, per warp
-    long long cur_tile;            // service warp -> compute warps (-1: no more tiles)
+    // per warp, double-buffered by tile parity (one named barrier per tile separates writers from readers)
+    __align__(16) int wfirst[2][RL_WARPS];     // first run start in the warp's 4 KiB (tile relative), RL_TILE if none
+    __align__(16) int wlast[2][RL_WARPS];      // last run start, -1 if none
+    __align__(16) uint32_t wcnt[2][RL_WARPS];  // boundaries found by the warp's rows: all | those before n << 16
+    uint32_t store_upto[2];        // compute warps' common snapshot of n_ready
+    RleMeta meta[2];
+    long long cur_tile[RL_NBUF];   // service warp -> compute warps (-1: no more tiles)
+    uint32_t prev_byte[RL_NBUF];   // the byte before the tile
     uint32_t n_meta;               // service warp -> base warp: tiles whose pair count is posted
     uint32_t n_ready;              // base warp -> compute warps: tiles whose first slot is known
-    uint32_t store_upto;           // compute warps' common snapshot of n_ready
     uint32_t done;                 // service warp -> base warp: no more tiles
+    uint32_t role;                 // 0: this CTA is the grid's scanner
     RlePending q[RLE_Q];
 };
 
@@ -215,97 +237,121 @@ __device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t* p) { retu
 __device__ __forceinline__ void st_volatile_shared(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
 
 __global__ void __launch_bounds__(RLE_THREADS, RLE_CTAS_PER_SM)
-rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_t n_scan, uint32_t prev_phase, int has_prev,
-                 uint8_t* __restrict__ counts, uint8_t* __restrict__ values, size_t pair_cap, uint64_t* __restrict__ d_pairs,
-                 uint64_t* __restrict__ d1, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg, uint32_t* __restrict__ next_tile,
-                 long long tiles)
+rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_t n_scan,
+                 uint32_t prev_phase, int has_prev, uint8_t* __restrict__ counts, uint8_t* __restrict__ values, size_t pair_cap,
+                 uint64_t* __restrict__ d_pairs, uint64_t* __restrict__ d1, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg,
+                 uint32_t* __restrict__ next_tile, uint32_t* __restrict__ role, long long tiles)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t* const inbuf = smem;                       // [16 left halo][tile][pad]
-    uint8_t* const cnt8 = smem + RL_INBUF;             // ring of staged counts
-    uint8_t* const val8 = cnt8 + RL_RINGB;             // ring of staged values
-    __shared__ __align__(8) uint64_t full[RL_NSUB], freeb, p1_ready, p2_ready;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* const inb = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // two swizzled tile buffers
+    uint8_t* const val8 = inb + RL_NBUF * RL_TILE;     // ring of staged values
+    uint8_t* const pos8 = val8 + RL_RINGB;             // ring of staged positions (mod 256)
+    __shared__ __align__(8) uint64_t full[RL_NBUF][RL_WARPS], freeb[RL_NBUF], meta_bar[2], aux;
     __shared__ RleShared sh;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (blockIdx.x == 0) {  // the scanner CTA
-        if (warp == 0) scan_pair_counts(agg, inc, tiles, lane);
-        return;
-    }
     if (tid == 0) {
+        sh.role = atomicAdd(role, 1u);
 #pragma unroll
-        for (int s = 0; s < RL_NSUB; ++s) mbar_init(&full[s], 1);
-        mbar_init(&freeb, RL_WARPS);
-        mbar_init(&p1_ready, RL_WARPS);
-        mbar_init(&p2_ready, RL_WARPS);
+        for (int b = 0; b < RL_NBUF; ++b)
+#pragma unroll
+            for (int s = 0; s < RL_WARPS; ++s) mbar_init(&full[b][s], 1);
+        mbar_init(&freeb[0], RL_WARPS);
+        mbar_init(&freeb[1], RL_WARPS);
+        mbar_init(&meta_bar[0], 1);
+        mbar_init(&meta_bar[1], 1);
+        mbar_init(&aux, 1);
         fence_mbar_init();
         sh.n_meta = 0;
         sh.n_ready = 0;
         sh.done = 0;
     }
     __syncthreads();
+    if (sh.role == 0) {  // the first CTA that runs is the scanner
+        if (warp == 0) scan_pair_counts(agg, inc, tiles, lane);
+        return;
+    }
 
     if (warp == RL_WARPS) {
         // ================================ service warp ===========================================
-        long long next = 0;
-        if (lane == 0) next = atomicAdd(next_tile, 1u);
-        next = __shfl_sync(0xffffffffu, next, 0);
-        for (uint32_t k = 0;; ++k) {
-            const long long tile = next;
-            const uint32_t par = k & 1u;
-            if (k) mbar_wait(&freeb, (k - 1) & 1u);  // the compute warps are done with the input buffer
+        const long long rows_full = (long long)(n_avail / RL_ROW);  // rows the tensor map covers
+        const uint32_t tail_bytes = (uint32_t)(n_avail % RL_ROW);   // bytes of the partial row behind them (plain loads)
+        uint32_t aux_par = 0;
+        // takes the next tile id and starts its loads into buffer b; returns the id
+        auto start_tile = [&](int b) -> long long {
+            long long tile = 0;
+            if (lane == 0) tile = atomicAdd(next_tile, 1u);
+            tile = __shfl_sync(0xffffffffu, tile, 0);
             if (tile >= tiles) {
-                if (lane == 0) sh.cur_tile = -1;
+                if (lane == 0) sh.cur_tile[b] = -1;
                 __syncwarp();
-                if (lane < RL_NSUB) mbar_arrive(&full[lane]);
-                break;
+                if (lane < RL_WARPS) mbar_arrive(&full[b][lane]);
+                return tile;
             }
+            uint8_t* const buf = inb + b * RL_TILE;
             const size_t tbase = (size_t)tile * RL_TILE;
-            if (lane == 0) sh.cur_tile = tile;
-            {
-                const size_t want = dmin(tbase + RL_TILE, n_avail);  // end of the bytes of the tile that exist
-                const size_t hi16 = want & ~(size_t)15;
-                const size_t lo0 = tile > 0 ? tbase - 16 : tbase;
-                // the ragged end (< 16 bytes) and the byte "before" the stream: plain loads
-                if (lane < 15) {
-                    const size_t g = dmax(hi16, lo0) + lane;
-                    if (g < want) inbuf[16 + (g - tbase)] = in[g];
-                }
-                if (tile == 0 && lane == 15) inbuf[15] = has_prev ? in[0] : (uint8_t)~in[0];
-                __syncwarp();
-                if (lane < RL_NSUB) {
-                    const size_t lo = lane == 0 ? lo0 : tbase + (size_t)lane * RL_SUB;
-                    const size_t hi = dmin(tbase + (size_t)(lane + 1) * RL_SUB, hi16);
-                    if (hi > lo) {
-                        mbar_expect_tx(&full[lane], (uint32_t)(hi - lo));
-                        tma_load_1d(inbuf + 16 + ((long long)lo - (long long)tbase), in + lo, (uint32_t)(hi - lo), &full[lane]);
-                    } else {
-                        mbar_arrive(&full[lane]);
+            const long long row0 = tile * RL_THREADS;
+            if (lane == 0) sh.cur_tile[b] = tile;
+            __syncwarp();
+            // the box that holds the partial last row of the data (at most one per shard) goes through `aux`
+            const bool tail_here = tail_bytes != 0 && rows_full >= row0 && rows_full < row0 + RL_THREADS;
+            const int tail_part = tail_here ? (int)((rows_full - row0) >> 5) : -1;
+            if (lane < RL_WARPS) {
+                const bool have = rows_full > row0 + 32 * lane;  // at least one full row in this box (rows past the end read as 0)
+                if (lane == tail_part) {
+                    if (have) {
+                        mbar_expect_tx(&aux, RL_WSPAN);
+                        tma_load_rows(buf + lane * RL_WSPAN, &tmap, (int)(row0 + 32 * lane), &aux);
                     }
+                } else if (have) {
+                    if (lane == 0) mbar_expect_tx_only(&full[b][0], RL_WSPAN);  // lane 0 arrives below, with the byte before the tile
+                    else mbar_expect_tx(&full[b][lane], RL_WSPAN);
+                    tma_load_rows(buf + lane * RL_WSPAN, &tmap, (int)(row0 + 32 * lane), &full[b][lane]);
+                } else if (lane != 0) {
+                    mbar_arrive(&full[b][lane]);
+                }
 #if RLE_PF_LEAD
-                    // A CTA has one input buffer, so a tile pays its load latency in full: make that an L2 hit.  Whoever
-                    // loads tile t asks L2 for tile t + RLE_PF_LEAD (somebody else's, about one grid of tiles later).
-                    {
-                        const size_t pb = tbase + (size_t)RLE_PF_LEAD * RL_TILE + (size_t)lane * RL_SUB;
-                        const size_t pe = dmin(pb + RL_SUB, n_avail & ~(size_t)15);
-                        if (pe > pb) tma_prefetch_l2(in + pb, (uint32_t)(pe - pb));
-                    }
-#endif
+                // make the load of the tile one grid of tiles ahead an L2 hit (somebody else's tile)
+                {
+                    const size_t pb = tbase + (size_t)RLE_PF_LEAD * RL_TILE + (size_t)lane * RL_WSPAN;
+                    const size_t pe = dmin(pb + RL_WSPAN, n_avail & ~(size_t)15);
+                    if (pe > pb) tma_prefetch_l2(in + pb, (uint32_t)(pe - pb));
                 }
+#endif
             }
-            TRACE(0);
+            if (tail_here) {  // warp-uniform
+                if (rows_full > row0 + 32 * tail_part) {
+                    mbar_wait(&aux, aux_par);  // the box has landed (its rows past the end as zeros): now the partial row
+                    aux_par ^= 1u;
+                }
+                const uint32_t r = (uint32_t)(rows_full - row0);
+                for (uint32_t i = lane; i < tail_bytes; i += 32) buf[swz(r, i)] = in[(size_t)rows_full * RL_ROW + i];
+                __syncwarp();
+                if (lane == 0 && tail_part != 0) mbar_arrive(&full[b][tail_part]);
+            }
+            if (lane == 0) {
+                // the byte before the tile; "before" the stream: a byte that differs from in[0] unless a run is open
+                sh.prev_byte[b] = tile > 0 ? in[tbase - 1] : (has_prev ? in[0] : (uint8_t)~in[0]);
+                mbar_arrive(&full[b][0]);
+            }
+            return tile;
+        };
+
+        long long cur = start_tile(0);
+        for (uint32_t k = 0;; ++k) {
+            const long long tile = cur;
+            if (tile >= tiles) break;
+            const uint32_t kb = k & 1u;
+            if (k) mbar_wait(&freeb[kb ^ 1u], ((k - 1) >> 1) & 1u);  // the compute warps are done with tile k-1: its buffer takes tile k+1
+            const long long nxt = start_tile((int)(kb ^ 1u));
+            const size_t tbase = (size_t)tile * RL_TILE;
             const uint32_t rel_emit = n > tbase ? (uint32_t)dmin((size_t)(n - tbase), (size_t)RL_TILE) : 0u;
-            const uint32_t rel_scan = (uint32_t)dmin((size_t)(n_scan - tbase), (size_t)RL_TILE);
-            const bool ragged = rel_emit < (uint32_t)RL_TILE || rel_scan < (uint32_t)RL_TILE;
-            // look-back #1 starts at once: it does not depend on this tile (the compute warps publish d1[tile] themselves)
             uint64_t sbB = prev_phase ? RL_BIAS - prev_phase : 0;   // biased start of the run that enters the tile
             if (tile > 0) sbB = lookback_run_start(d1, tile, lane);
-            TRACE(1);
-            mbar_wait(&p1_ready, par);  // chunk_first / chunk_last are posted
-            const int cf = lane < RL_NCHUNK ? sh.chunk_first[lane] : RL_TILE;
-            const int cl = lane < RL_NCHUNK ? sh.chunk_last[lane] : -1;
-            const int F_t = __reduce_min_sync(0xffffffffu, cf);   // first run start of the tile, RL_TILE if none
-            const int L_t = __reduce_max_sync(0xffffffffu, cl);   // last run start, -1 if none
+            mbar_wait(&meta_bar[kb], (k >> 1) & 1u);  // the compute warps have counted the tile
+            const int F_t = sh.meta[kb].first_start;
+            const int L_t = sh.meta[kb].last_start;
+            const uint32_t total_emit = sh.meta[kb].total_emit;
             if (L_t < 0 && lane == 0) st_relaxed_u64(d1 + tile, LB_INC | sbB);  // no run starts here: pass the entering one on
             // boundaries of the entering run: sb + 255 j.  All positions biased by RL_BIAS so they stay non-negative.
             const uint64_t tB = tbase + RL_BIAS;                    // biased tile base; sbB < tB always
@@ -316,10 +362,7 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             const uint32_t nl_all = (uint32_t)((FB - 1 - sbB) / 255u - q0);
             const uint32_t nl = limB > tB ? (uint32_t)((limB - 1 - sbB) / 255u - q0) : 0u;
             const uint32_t lagged = nl_all ? 255u : (uint32_t)(FB - BpB);  // count of the last pair before this tile
-            mbar_wait(&p2_ready, par);  // chunk_cnt (and emit_cnt) are posted
-            TRACE(3);
-            const uint32_t mine = ragged ? (lane < RL_WARPS ? sh.emit_cnt[lane] : 0u) : (lane < RL_NCHUNK ? sh.chunk_cnt[lane] : 0u);
-            const uint32_t tot = nl + __reduce_add_sync(0xffffffffu, mine);
+            const uint32_t tot = nl + total_emit;
             if (lane == 0) {
                 st_relaxed_u32(agg + tile, 0x80000000u | tot);  // to the scanner
                 RlePending& e = sh.q[k % RLE_Q];
@@ -334,11 +377,9 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
                 e.lagged = (tile > 0 && BpB < n + RL_BIAS) ? lagged : 0u;
                 __threadfence_block();
                 st_volatile_shared(&sh.n_meta, k + 1);
-                // the next tile id: taken late, so that tiles start (and publish) nearly in id order, yet it is here
-                // before the compute warps release the input buffer
-                next = atomicAdd(next_tile, 1u);
             }
-            next = __shfl_sync(0xffffffffu, next, 0);
+            __syncwarp();
+            cur = nxt;
         }
         if (lane == 0) {
             __threadfence_block();
@@ -371,9 +412,6 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             if (lane < rr) {
                 g &= ~(1ull << 63);
                 e.g0 = g;
-#ifdef FLRL_TRACE
-                if (g_rle_trace) g_rle_trace[(size_t)e.tile * 16 + 5] = gtime();
-#endif
                 if (e.lagged && g >= 1 && g - 1 < pair_cap) counts[g - 1] = (uint8_t)e.lagged;
                 if (e.tile == tiles - 1) *d_pairs = g + e.tot;
             }
@@ -393,11 +431,14 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
 
     // ================================= compute warps =======================================
     const uint32_t lt_mask = (1u << lane) - 1u;
+    const uint32_t sw = (uint32_t)tid & 7u;       // swizzle of this thread's row
+    const int rowstart = tid * RL_ROW;            // tile-relative position of the row
     uint32_t n_stored = 0;   // tiles of this CTA already written to global memory
-    uint32_t ring_head = 0;  // ring position after the last staged pair (not masked)
+    uint32_t ring_head = 0;  // ring position after the last staged boundary (not masked)
 
     // writes a tile whose first slot is known: the pairs at 255-splits before its first run start (long runs only),
-    // then its staged pairs.  The tile's last count is left to the next tile (it knows where the next boundary is).
+    // then its staged pairs.  The tile's last count is left to the next tile (it knows where the next boundary is)
+    // unless a boundary past n is staged behind it.
     auto store_tile = [&](const RlePending& e) {
         const uint32_t nl = e.nl;
         const bool lead_lag = e.nl_all == nl && e.total_all == 0;  // the last split is the tile's last boundary
@@ -410,8 +451,8 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             }
         }
         if (e.total) {
-            store_from_ring(values, e.g0 + nl, e.total, pair_cap, val8, e.head, tid);
-            store_from_ring(counts, e.g0 + nl, e.total - 1u, pair_cap, cnt8, e.head, tid);
+            store_from_ring<false>(values, e.g0 + nl, e.total, pair_cap, val8, e.head, tid);
+            store_from_ring<true>(counts, e.g0 + nl, e.total_all > e.total ? e.total : e.total - 1u, pair_cap, pos8, e.head, tid);
         }
     };
     // blocks until the first slots of the CTA's first `need` tiles are known; returns how many are (>= need)
@@ -421,22 +462,26 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
             uint32_t r;
             while ((r = ld_volatile_shared(&sh.n_ready)) < need) __nanosleep(RLE_SLEEP_A);
             __threadfence_block();
-            sh.store_upto = r;
+            sh.store_upto[0] = r;
         }
         bar_sync(BAR_COMPUTE, RL_THREADS);
-        return sh.store_upto;
+        const uint32_t r = sh.store_upto[0];
+        bar_sync(BAR_COMPUTE, RL_THREADS);  // ... before the slot is reused
+        return r;
     };
 
     for (uint32_t k = 0;; ++k) {
-        const uint32_t par = k & 1u;
+        const uint32_t kb = k & 1u, fpar = (k >> 1) & 1u;
         if (k - n_stored >= (uint32_t)RLE_Q - 1u) {  // the queue of waiting tiles is full (rare)
             const uint32_t upto = wait_ready(n_stored + 1u);
             for (; n_stored < upto; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
         }
-#pragma unroll
-        for (int s = 0; s < RL_NSUB; ++s) mbar_wait(&full[s], par);  // the whole tile: the four mask computations below interleave
-        const long long tile = *reinterpret_cast<const volatile long long*>(&sh.cur_tile);
+        if (warp > 0) mbar_wait(&full[kb][warp - 1], fpar);  // the last byte of the previous warp's rows
+        mbar_wait(&full[kb][warp], fpar);
+        const long long tile = *reinterpret_cast<const volatile long long*>(&sh.cur_tile[kb]);
         if (tile < 0) break;
+        const uint8_t* const buf = inb + kb * RL_TILE;
+        const uint8_t* const rowp = buf + rowstart;
         const size_t tbase = (size_t)tile * RL_TILE;
         // tile-relative limits: positions >= rel_emit are not emitted; position rel_scan is a forced boundary (the end
         // of the data, or far enough into the look-ahead that every emitted pair has its count), nothing after it counts
@@ -444,144 +489,146 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
         const uint32_t rel_scan = (uint32_t)dmin((size_t)(n_scan - tbase), (size_t)RL_TILE);  // == RL_TILE: not in this tile
         const bool ragged = rel_emit < (uint32_t)RL_TILE || rel_scan < (uint32_t)RL_TILE;
 
-        uint32_t bm[RL_NSUB];     // phase 1: run-start mask; phase 2 on: all pair boundaries of the segment
-        int sprev[RL_NSUB];       // phase 1: nearest earlier run start inside the warp (-1 none); phase 2 on: last boundary before the segment
-        uint32_t slot[RL_NSUB];   // first staged slot of the segment (tile relative)
-
-        // ---- phase 1: run-start masks, nearest earlier run start by ballot.  The LAST sub-tile goes first: the next
-        // tile's look-back #1 only needs this tile's last run start, which is published the moment it is known
-        if (warp == 0) TRACE(8);
-#pragma unroll
-        for (int i = 0; i < RL_NSUB; ++i) {
-            const int s = (i + RL_NSUB - 1) % RL_NSUB;
-            const int off = s * RL_SUB + tid * RL_SEG;
-            uint32_t m = segment_mask(inbuf, off);
-            if (ragged) {  // CTA-uniform: only the last tiles see the end of the data
-                const int kk = (int)rel_scan - off;
-                if (kk < 0) m = 0;
-                else if (kk < 32) m = (m & ((1u << kk) - 1u)) | (1u << kk);
-            }
-            const unsigned bal = __ballot_sync(0xffffffffu, m != 0);
-            const int my_last = off + 31 - __clz(m);
-            const unsigned lower = bal & lt_mask;
-            const int S = __shfl_sync(0xffffffffu, my_last, 31 - __clz(lower | 1u));
-            sprev[s] = lower ? S : -1;
-            bm[s] = m;
-            const int wc = s * RL_WARPS + warp;
-            if (m != 0 && lower == 0) sh.chunk_first[wc] = off + __ffs(m) - 1;
-            if (m != 0 && (bal >> lane) == 1u) {
-                sh.chunk_last[wc] = my_last;
-                if (wc == RL_NCHUNK - 1) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + my_last + RL_BIAS));
-            }
-            if (bal == 0 && lane == 0) {
-                sh.chunk_first[wc] = RL_TILE;
-                sh.chunk_last[wc] = -1;
-            }
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&p1_ready);
-        if (warp == 0) TRACE(9);
-        bar_sync(BAR_COMPUTE, RL_THREADS);  // #1
-
-        // ---- phase 2: the one possible 255-split of each segment, pair counts
+        // ---- step A: the row's run-start mask, its 255-split, pair counts; nothing from other warps is needed
+        uint32_t M[4];
         {
-            const int cl = lane < RL_NCHUNK ? sh.chunk_last[lane] : -1;
-            const unsigned b2 = __ballot_sync(0xffffffffu, cl >= 0);
-            if (warp == 0 && !(b2 >> (RL_NCHUNK - 1))) {
-                // the tile's last 1 KiB held no run start, so d1[tile] is still empty: last run start of the tile, or "none"
-                // (the service warp replaces "none" by the entering run's start once it knows it)
-                const int L_t = __reduce_max_sync(0xffffffffu, cl);
-                if (lane == 0) {
-                    if (L_t >= 0) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + L_t + RL_BIAS));
-                    else if (tile > 0) atomicMax(reinterpret_cast<unsigned long long*>(d1 + tile), (unsigned long long)LB_AGG);  // never undoes the final value
-                }
-            }
-            uint32_t cn[RL_NSUB / 2], cne = 0;
+            // the word that ends with the byte before the row (only its top byte is used)
+            uint32_t pw = tid == 0 ? ld_volatile_shared(&sh.prev_byte[kb]) << 24
+                                   : *reinterpret_cast<const uint32_t*>(buf + (rowstart - RL_ROW) + (((7u ^ (uint32_t)(tid - 1)) & 7u) << 4) + 12);
 #pragma unroll
-            for (int s = 0; s < RL_NSUB; ++s) {
-                const int off = s * RL_SUB + tid * RL_SEG;
-                const int wc = s * RL_WARPS + warp;
-                const unsigned lowerb = b2 & ((1u << wc) - 1u);
-                const int Sin = __shfl_sync(0xffffffffu, cl, 31 - __clz(lowerb | 1u));
-                int S = sprev[s];
-                if (S < 0 && lowerb) S = Sin;
-                uint32_t bb = bm[s];
-                if (S >= 0) {
-                    const uint32_t lead = bb ? (uint32_t)(__ffs(bb) - 1) : 32u;  // bytes that continue the entering run
-                    if ((uint32_t)(off - S) + lead > 255u) {
-                        // boundaries of the entering run lie at S + 255 j; r = distance from the last one to off - 1
-                        const uint32_t r = (uint32_t)(off - 1 - S) % 255u;
-                        const uint32_t j = 254u - r;
-                        if (j < lead) bb |= 1u << j;
-                        S = off - 1 - (int)r;
-                    }
-                }
-                sprev[s] = S;  // last boundary before the segment (or -1: none in this tile)
-                bm[s] = bb;
-                if (s & 1) cn[s >> 1] |= __popc(bb) << 16;
-                else cn[s >> 1] = __popc(bb);
-                if (ragged) {
-                    const int kk = (int)rel_emit - off;
-                    const uint32_t em = kk <= 0 ? 0u : (kk >= 32 ? ~0u : ((1u << kk) - 1u));
-                    cne += __popc(bb & em);
-                }
-            }
-#pragma unroll
-            for (int h = 0; h < RL_NSUB / 2; ++h) {
-                uint32_t inc2 = cn[h];
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const uint32_t o = __shfl_up_sync(0xffffffffu, inc2, d);
-                    if (lane >= d) inc2 += o;
-                }
-                if (lane == 31) {
-                    sh.chunk_cnt[(2 * h) * RL_WARPS + warp] = inc2 & 0xffffu;
-                    sh.chunk_cnt[(2 * h + 1) * RL_WARPS + warp] = inc2 >> 16;
-                }
-                const uint32_t ex = inc2 - cn[h];
-                slot[2 * h] = ex & 0xffffu;
-                slot[2 * h + 1] = ex >> 16;
-            }
-            if (ragged) {
-                cne = __reduce_add_sync(0xffffffffu, cne);
-                if (lane == 0) sh.emit_cnt[warp] = cne;
+            for (int g = 0; g < 4; ++g) {
+                const uint4 a = *reinterpret_cast<const uint4*>(rowp + (((2u * g) ^ sw) << 4));
+                const uint4 c = *reinterpret_cast<const uint4*>(rowp + (((2u * g + 1u) ^ sw) << 4));
+                const uint32_t w[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+                M[g] = start_mask32(w, pw);
+                pw = c.w;
             }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&p2_ready);
+        if (ragged) {  // CTA-uniform: only the last tiles see the end of the data
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const int kk = (int)rel_scan - (rowstart + 32 * g);
+                if (kk < 0) M[g] = 0;
+                else if (kk < 32) M[g] = (M[g] & ((1u << kk) - 1u)) | (1u << kk);
+            }
+        }
+        const uint32_t any = M[0] | M[1] | M[2] | M[3];
+        const unsigned bal = __ballot_sync(0xffffffffu, any != 0);
+        // bytes of the row that continue the entering run / last run start of the row (tile relative)
+        const int lead = M[0] ? __ffs(M[0]) - 1 : M[1] ? 31 + __ffs(M[1]) : M[2] ? 63 + __ffs(M[2]) : M[3] ? 95 + __ffs(M[3]) : RL_ROW;
+        const int my_last = rowstart + (M[3] ? 127 - __clz(M[3]) : M[2] ? 95 - __clz(M[2]) : M[1] ? 63 - __clz(M[1]) : 31 - __clz(M[0]));
+        const unsigned lower = bal & lt_mask;
+        const int S = __shfl_sync(0xffffffffu, my_last, 31 - __clz(lower | 1u));  // nearest run start before the row, if lower != 0
+        if (lower != 0 && (rowstart - S) + lead > 255 && !(ragged && rowstart > (int)rel_scan)) {
+            // boundaries of the entering run lie at S + 255 j; rr = distance from the last one to rowstart - 1
+            const uint32_t rr = (uint32_t)(rowstart - 1 - S) % 255u;
+            const uint32_t j = 254u - rr;
+            if (j < (uint32_t)lead) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                    if ((j >> 5) == (uint32_t)g) M[g] |= 1u << (j & 31u);
+            }
+        }
+        uint32_t packed = __popc(M[0]) + __popc(M[1]) + __popc(M[2]) + __popc(M[3]);  // <= 128; a warp's sum <= 4096
+        if (ragged) {
+            uint32_t ce = 0;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const int kk = (int)rel_emit - (rowstart + 32 * g);
+                const uint32_t em = kk <= 0 ? 0u : (kk >= 32 ? ~0u : ((1u << kk) - 1u));
+                ce += __popc(M[g] & em);
+            }
+            packed |= ce << 16;
+        } else {
+            packed |= packed << 16;
+        }
+        uint32_t incl = packed;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        const uint32_t excl = (incl - packed) & 0xffffu;  // boundaries of the warp's earlier rows
+        if (lane == 31) sh.wcnt[kb][warp] = incl;
+        if (bal) {
+            if (lane == __ffs(bal) - 1) sh.wfirst[kb][warp] = rowstart + lead;  // this row has no split: lead is its first run start
+            if (lane == 31 - __clz(bal)) {
+                sh.wlast[kb][warp] = my_last;
+                // the next tile's look-back #1 only needs this tile's last run start: published the moment it is known
+                if (warp == RL_WARPS - 1) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + my_last + RL_BIAS));
+            }
+        } else if (lane == 0) {
+            sh.wfirst[kb][warp] = RL_TILE;
+            sh.wlast[kb][warp] = -1;
+        }
         if (tid == 0) {  // which of the waiting tiles can be written after this tile's compaction
             const uint32_t r = ld_volatile_shared(&sh.n_ready);
             __threadfence_block();
-            sh.store_upto = r;
+            sh.store_upto[kb] = r;
         }
-        if (warp == 0) TRACE(10);
-        bar_sync(BAR_COMPUTE, RL_THREADS);  // #2
-        uint32_t upto = sh.store_upto;
+        bar_sync(BAR_COMPUTE, RL_THREADS);
+        uint32_t upto = sh.store_upto[kb];
 
-        // ---- phase 3: slots, compaction (values + lagged counts) into the ring
-        uint32_t total_all, total_emit;
+        // ---- step B: every warp derives the same tile layout from the four warps' (first, last, count):
+        // the splits in a warp's leading rows (closed form from the previous warps' last run start), bases, totals
+        uint32_t total_all = 0, total_emit = 0, mybase = 0, mynl = 0, myfirst = 0;
+        int F_t, L_t, L_lastwarp;
         {
-            const uint32_t cc = lane < RL_NCHUNK ? sh.chunk_cnt[lane] : 0u;
-            uint32_t csum = cc;
+            const int4 Fv = *reinterpret_cast<const int4*>(sh.wfirst[kb]);
+            const int4 Lv = *reinterpret_cast<const int4*>(sh.wlast[kb]);
+            const uint4 Cv = *reinterpret_cast<const uint4*>(sh.wcnt[kb]);
+            const int Fa[4] = {Fv.x, Fv.y, Fv.z, Fv.w}, La[4] = {Lv.x, Lv.y, Lv.z, Lv.w};
+            const uint32_t Ca[4] = {Cv.x, Cv.y, Cv.z, Cv.w};
+            int Srun = -1;
 #pragma unroll
-            for (int d = 1; d < RL_NCHUNK; d <<= 1) {
-                const uint32_t o = __shfl_up_sync(0xffffffffu, csum, d);
-                if (lane >= d) csum += o;
+            for (int i = 0; i < RL_WARPS; ++i) {
+                const int ws = RL_WSPAN * i;
+                uint32_t nl_i = 0, nle_i = 0, first_i = 0;
+                if (i > 0 && Srun >= 0 && !(ragged && ws > (int)rel_scan)) {
+                    const int end_i = min(Fa[i], ws + RL_WSPAN);
+                    const uint32_t q0 = (uint32_t)(ws - 1 - Srun) / 255u;
+                    nl_i = (uint32_t)(end_i - 1 - Srun) / 255u - q0;
+                    first_i = (uint32_t)Srun + 255u * (q0 + 1u);
+                    nle_i = nl_i;
+                    if (ragged) {
+                        const int end_e = min(end_i, (int)rel_emit);
+                        nle_i = end_e > ws ? (uint32_t)(end_e - 1 - Srun) / 255u - q0 : 0u;
+                    }
+                }
+                if (i == warp) {
+                    mybase = total_all;
+                    mynl = nl_i;
+                    myfirst = first_i;
+                }
+                total_all += nl_i + (Ca[i] & 0xffffu);
+                total_emit += nle_i + (Ca[i] >> 16);
+                if (La[i] >= 0) Srun = La[i];
             }
-            total_all = __shfl_sync(0xffffffffu, csum, RL_NCHUNK - 1);
-            total_emit = total_all;
-            if (ragged) {
-                const uint32_t e = lane < RL_WARPS ? sh.emit_cnt[lane] : 0u;
-                total_emit = __reduce_add_sync(0xffffffffu, e);
-            }
-            const uint32_t excl = csum - cc;
-#pragma unroll
-            for (int s = 0; s < RL_NSUB; ++s) slot[s] += __shfl_sync(0xffffffffu, excl, s * RL_WARPS + warp);
+            F_t = min(min(Fa[0], Fa[1]), min(Fa[2], Fa[3]));
+            L_t = max(max(La[0], La[1]), max(La[2], La[3]));
+            L_lastwarp = La[RL_WARPS - 1];
         }
         RlePending& me = sh.q[k % RLE_Q];
-        const bool deferred = total_all == total_emit && total_all <= (uint32_t)RL_RING;
-        if (deferred) {
-            // room in the ring?  (the oldest waiting tile's pairs start at its `head`)
+        if (tid == 0) {
+            // the tile's last 4 KiB held no run start, so d1[tile] is still empty: last run start of the tile, or "none"
+            // (the service warp replaces "none" by the entering run's start once it knows it)
+            if (L_lastwarp < 0) {
+                if (L_t >= 0) st_relaxed_u64(d1 + tile, LB_INC | (uint64_t)(tbase + L_t + RL_BIAS));
+                else if (tile > 0) atomicMax(reinterpret_cast<unsigned long long*>(d1 + tile), (unsigned long long)LB_AGG);  // never undoes the final value
+            }
+            sh.meta[kb].first_start = F_t;
+            sh.meta[kb].last_start = L_t;
+            sh.meta[kb].total_all = total_all;
+            sh.meta[kb].total_emit = total_emit;
+            mbar_arrive(&meta_bar[kb]);  // release: the service warp reads the four words above
+            me.total_all = total_all;
+            me.first_byte = buf[0];
+        }
+
+        // ---- compaction: value and position of every boundary into the ring
+        const uint32_t wbyte = buf[warp * RL_WSPAN];  // value of the run that enters the warp's rows
+        if (total_all <= (uint32_t)RL_RING) {
+            // room in the ring?  (the oldest waiting tile's boundaries start at its `head`)
             if (n_stored < k && ring_head + total_all - sh.q[n_stored % RLE_Q].head > (uint32_t)RL_RING) {
                 do {
                     upto = wait_ready(n_stored + 1u);
@@ -589,78 +636,88 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
                 } while (n_stored < k && ring_head + total_all - sh.q[n_stored % RLE_Q].head > (uint32_t)RL_RING);
                 bar_sync(BAR_COMPUTE, RL_THREADS);  // every warp has read the ring space that is written next
             }
+            const uint32_t wb = ring_head + mybase;
+            for (uint32_t j = lane; j < mynl; j += 32) {  // splits in the warp's leading rows
+                const uint32_t idx = (wb + j) & (RL_RING - 1);
+                const uint8_t p8 = (uint8_t)(myfirst + 255u * j);
+                val8[idx] = (uint8_t)wbyte;
+                pos8[idx] = p8;
+                if (idx == 0) pos8[RL_RING] = p8;
+            }
+            const uint32_t kk0 = wb + mynl + excl;
+            uint32_t kk = kk0;
 #pragma unroll
-            for (int s = 0; s < RL_NSUB; ++s) {
-                const int off = s * RL_SUB + tid * RL_SEG;
-                const uint8_t* src = inbuf + 16 + off;
-                uint32_t bits = bm[s], kk = slot[s];
-                int prevpos = sprev[s];
+            for (int g = 0; g < 4; ++g) {
+                uint32_t bits = M[g];
                 while (bits) {
-                    const int bi = __ffs(bits) - 1;
+                    const uint32_t p = 32u * g + (uint32_t)__ffs(bits) - 1u;
                     bits &= bits - 1;
-                    val8[(ring_head + kk) & (RL_RING - 1)] = src[bi];
-                    if (kk) cnt8[(ring_head + kk - 1u) & (RL_RING - 1)] = (uint8_t)(off + bi - prevpos);
-                    prevpos = off + bi;
+                    const uint32_t idx = kk & (RL_RING - 1);
+                    val8[idx] = rowp[((((p >> 4) ^ sw) & 7u) << 4) | (p & 15u)];
+                    pos8[idx] = (uint8_t)(rowstart + p);
                     ++kk;
                 }
             }
+            // entry RL_RING mirrors entry 0 (a count is the difference of neighbouring positions)
+            if (kk != kk0 && (((kk - 1u) ^ (kk0 - 1u)) & ~(uint32_t)(RL_RING - 1))) pos8[RL_RING] = pos8[0];
             if (tid == 0) {
                 me.head = ring_head;
-                me.total = total_all;
-                me.total_all = total_all;
-                me.first_byte = inbuf[16];
+                me.total = total_emit;
             }
             ring_head += total_all;
             __syncwarp();
-            if (lane == 0) mbar_arrive(&freeb);  // the input buffer may be refilled
-            if (warp == 0) TRACE(12);
+            if (lane == 0) mbar_arrive(&freeb[kb]);  // the tile buffer may be refilled
             for (; n_stored < upto && n_stored < k; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
         } else {
-            // rare: a ragged last tile, or more pairs than the ring holds -> written at once, in rounds, after
-            // everything that waits
+            // rare: more boundaries than the ring holds -> written at once, in rounds, after everything that waits
             if (tid == 0) {
-                me.head = ring_head;
+                me.head = 0;
                 me.total = 0;
-                me.total_all = total_all;
-                me.first_byte = inbuf[16];
             }
             upto = wait_ready(k + 1u);
             for (; n_stored < k; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
             store_tile(me);  // its pairs at 255-splits before the first run start
             const uint64_t g0 = me.g0 + me.nl;
+            const uint32_t rel0 = mybase + mynl + excl;  // tile-relative index of the row's first boundary
             for (uint32_t w0 = 0; w0 < total_emit; w0 += RL_RING) {
                 bar_sync(BAR_COMPUTE, RL_THREADS);  // the ring is free (previous round / earlier tiles have been read)
+                // boundaries w0 .. w0 + RL_RING (the last one only as the end of the count before it)
+                for (uint32_t j = lane; j < mynl; j += 32) {
+                    const uint32_t q = mybase + j - w0;
+                    if (q <= (uint32_t)RL_RING) {
+                        val8[q] = (uint8_t)wbyte;
+                        pos8[q] = (uint8_t)(myfirst + 255u * j);
+                    }
+                }
+                uint32_t q = rel0 - w0;
 #pragma unroll
-                for (int s = 0; s < RL_NSUB; ++s) {
-                    const int off = s * RL_SUB + tid * RL_SEG;
-                    const uint8_t* src = inbuf + 16 + off;
-                    uint32_t bits = bm[s], kk = slot[s];
-                    int prevpos = sprev[s];
+                for (int g = 0; g < 4; ++g) {
+                    uint32_t bits = M[g];
                     while (bits) {
-                        const int bi = __ffs(bits) - 1;
+                        const uint32_t p = 32u * g + (uint32_t)__ffs(bits) - 1u;
                         bits &= bits - 1;
-                        if (kk >= w0 && kk < w0 + RL_RING && kk < total_emit) val8[kk - w0] = src[bi];
-                        if (kk > w0 && kk <= w0 + RL_RING && kk <= total_emit) cnt8[kk - 1 - w0] = (uint8_t)(off + bi - prevpos);
-                        prevpos = off + bi;
-                        ++kk;
+                        if (q <= (uint32_t)RL_RING) {
+                            val8[q] = rowp[((((p >> 4) ^ sw) & 7u) << 4) | (p & 15u)];
+                            pos8[q] = (uint8_t)(rowstart + p);
+                        }
+                        ++q;
                     }
                 }
                 bar_sync(BAR_COMPUTE, RL_THREADS);
                 const uint32_t cw = min((uint32_t)RL_RING, total_emit - w0);
-                const bool tail = w0 + cw == total_emit && total_all == total_emit;  // that count is written by the next tile
-                store_compacted(values, g0 + w0, cw, pair_cap, val8, 0, tid);
-                store_compacted(counts, g0 + w0, cw - (tail ? 1u : 0u), pair_cap, cnt8, 0, tid);
+                const bool has_next = w0 + cw < total_all;  // else that count is written by the next tile
+                store_compacted<false>(values, g0 + w0, cw, pair_cap, val8, 0, tid);
+                store_compacted<true>(counts, g0 + w0, cw - (has_next ? 0u : 1u), pair_cap, pos8, 0, tid);
             }
             n_stored = k + 1u;
             bar_sync(BAR_COMPUTE, RL_THREADS);  // the ring has been read
             ring_head = 0;
-            if (lane == 0) mbar_arrive(&freeb);
+            if (lane == 0) mbar_arrive(&freeb[kb]);
         }
-        if (warp == 0) TRACE(14);
     }
     // ---- the tiles that still wait
     {
-        const uint32_t k_end = ld_volatile_shared(&sh.n_meta);  // == tiles taken by this CTA (every one of them passed p2)
+        const uint32_t k_end = ld_volatile_shared(&sh.n_meta);  // == tiles taken by this CTA (every one of them was counted)
         if (n_stored < k_end) {
             wait_ready(k_end);
             for (; n_stored < k_end; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
@@ -675,6 +732,23 @@ rl_encode_kernel(const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_
 size_t rl_encode_tiles(size_t n) { return (((n + 255) / RL_TILE + 1) + 255) / 256 * 256; }  // padded: the scanner works on whole chunks
 size_t rl_encode_workspace_bytes(size_t n) { return (3 * rl_encode_tiles(n) + 2) * sizeof(uint64_t); }
 
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn()
+{
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+}  // namespace
+
 cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint64_t prev_run, uint8_t* d_counts,
                              uint8_t* d_values, size_t pair_cap, uint64_t* d_pairs, void* d_ws, cudaStream_t stream)
 {
@@ -685,40 +759,49 @@ cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint
     uint64_t* inc = d1 + tmax;                          // first slots (scanner -> tiles)
     uint32_t* agg = reinterpret_cast<uint32_t*>(inc + tmax);  // pair counts (tiles -> scanner)
     uint32_t* next_tile = agg + tmax;                   // tile counter
+    uint32_t* role = next_tile + 1;                     // role counter: the first CTA that runs is the scanner
     cudaError_t e = cudaMemsetAsync(d_ws, 0, rl_encode_workspace_bytes(n), stream);
     if (e != cudaSuccess) return e;
-    constexpr int smem = RL_INBUF + 2 * RL_RINGB;
-    // the grid must be fully co-resident: the tiles wait for the scanner CTA, the scanner for every tile taken
+    // the input as rows of 128 bytes; the partial last row is loaded with plain loads
+    CUtensorMap tmap;
+    memset(&tmap, 0, sizeof tmap);
+    const size_t rows_full = n_avail / RL_ROW;
+    if (rows_full) {
+        EncodeTiledFn enc = encode_tiled_fn();
+        if (!enc) return cudaErrorNotSupported;
+        if (rows_full > 0x7fffffffull) return cudaErrorInvalidValue;  // 256 GiB per call
+        const cuuint64_t gdim[2] = {RL_ROW, rows_full};
+        const cuuint64_t gstride[1] = {RL_ROW};
+        const cuuint32_t box[2] = {RL_ROW, 32};
+        const cuuint32_t estr[2] = {1, 1};
+        if (enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(d_in), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return cudaErrorInvalidValue;
+    }
     int dev = 0;
     e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     static int resident[64];
     int cap = dev < 64 ? resident[dev] : 0;
     if (!cap) {
-        e = cudaFuncSetAttribute((const void*)rl_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        e = cudaFuncSetAttribute((const void*)rl_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RLE_SMEM);
         if (e != cudaSuccess) return e;
         int sms = 0, per_sm = 0;
         e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)rl_encode_kernel, RLE_THREADS, smem);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)rl_encode_kernel, RLE_THREADS, RLE_SMEM);
         if (e != cudaSuccess) return e;
         if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-        static const int want = getenv("FLRL_RLE_CTAS") ? atoi(getenv("FLRL_RLE_CTAS")) : RLE_CTAS_PER_SM;
-        cap = sms * std::max(1, std::min(per_sm, want));
+        cap = sms * std::max(1, std::min(per_sm, RLE_CTAS_PER_SM));
         if (cap < 2) return cudaErrorLaunchOutOfResources;
         if (dev < 64) resident[dev] = cap;
     }
-    const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap - 1) + 1;  // the scanner CTA + the workers
-    rl_encode_kernel<<<grid, RLE_THREADS, smem, stream>>>(d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), prev_run != 0, d_counts,
-                                                          d_values, pair_cap, d_pairs, d1, inc, agg, next_tile, (long long)tiles);
+    // one CTA becomes the scanner, the others take tiles; CTAs that are not resident at once simply start later
+    const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap - 1) + 1;
+    rl_encode_kernel<<<grid, RLE_THREADS, RLE_SMEM, stream>>>(tmap, d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), prev_run != 0,
+                                                              d_counts, d_values, pair_cap, d_pairs, d1, inc, agg, next_tile, role,
+                                                              (long long)tiles);
     return cudaGetLastError();
 }
 
 }  // namespace flrl
-
-#ifdef FLRL_TRACE
-extern "C" int flrl_debug_set_rle_trace(void* d_buf)
-{
-    return (int)cudaMemcpyToSymbol(flrl::g_rle_trace, &d_buf, sizeof(d_buf));
-}
-#endif

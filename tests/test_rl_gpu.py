@@ -54,15 +54,17 @@ def test_rl_empty(flrl):
     assert out.numel() == 0
 
 
-@pytest.mark.parametrize("run", [1, 2, 254, 255, 256, 509, 510, 511, 765, 766, 8191, 8192, 8193, 8192 + 255, 100000])
+@pytest.mark.parametrize("run", [1, 2, 127, 128, 129, 254, 255, 256, 509, 510, 511, 765, 766, 4095, 4096, 4097, 4096 + 255, 8191, 8192, 8193,
+                                 8192 + 255, 16383, 16384, 16385, 16384 + 255, 32768 + 254, 100000])
 def test_rl_long_run_split(run, oracle, flrl):
-    """Greedy 255-split, also across tile boundaries (8 KiB tiles)."""
+    """Greedy 255-split, also across row (128 B), warp (4 KiB) and tile (16 KiB) boundaries."""
     _check(flrl, oracle, np.frombuffer(bytes([9]) * run + b"\x01", dtype=np.uint8))
     _check(flrl, oracle, np.frombuffer(b"\x07\x07\x03" + bytes([9]) * run, dtype=np.uint8))
 
 
-@pytest.mark.parametrize("n", [1, 2, 15, 16, 17, 31, 32, 33, 255, 256, 257, 8191, 8192, 8193, 8192 + 256, 8192 * 2 - 1,
-                               8192 * 3 + 77, 65537, 300001, (1 << 20) + 5])
+@pytest.mark.parametrize("n", [1, 2, 15, 16, 17, 31, 32, 33, 127, 128, 129, 255, 256, 257, 4095, 4096, 4097, 8191, 8192, 8193, 8192 + 256,
+                               8192 * 2 - 1, 16384, 16385, 16384 + 127, 16384 + 128, 16384 * 2 - 255, 16384 * 2 - 1, 8192 * 3 + 77, 65537,
+                               300001, (1 << 20) + 5])
 @pytest.mark.parametrize("mean", [1.3, 4, 64, 700])
 def test_rl_ragged_sizes(n, mean, oracle, flrl):
     _check(flrl, oracle, _runs(np.random.default_rng(n + int(mean * 10)), n, mean))
