@@ -49,6 +49,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
     }
 }
 
+// the same for a warp that waits long and has nothing else to do (service warps): long pauses between looks
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns = 200)
+{
+    while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
+
 // global -> shared bulk copy; bytes % 16 == 0, both addresses 16-byte aligned.
 __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar)
 {

@@ -49,23 +49,23 @@ namespace flrl {
 
 static constexpr int RL_WARPS = 4;                      // compute warps
 static constexpr int RL_THREADS = RL_WARPS * 32;        // compute threads = rows per tile
-static constexpr int RLE_THREADS = RL_THREADS + 64;     // + service warp + base warp
+static constexpr int RLE_THREADS = RL_THREADS + 32;     // + service warp
 static constexpr int RL_ROW = 128;                      // bytes per thread and tile (the swizzle span)
 static constexpr int RL_TILE = RL_ROW * RL_THREADS;     // 16 KiB
 static constexpr int RL_WSPAN = RL_TILE / RL_WARPS;     // 4 KiB of consecutive bytes per warp = one TMA box of 32 rows
-static constexpr int RL_NBUF = 2;                       // tile buffers per CTA
+#ifndef RL_NBUF_N
+#define RL_NBUF_N 2
+#endif
+static constexpr int RL_NBUF = RL_NBUF_N;               // tile buffers per CTA (2: the next tile lands while this one is worked on)
 #ifndef RL_RING_PAIRS
 #define RL_RING_PAIRS 8192
 #endif
-// pause between two looks of a polling loop (ns): the base warp with nothing to hand out / with answers pending
+// pause between two looks of a polling loop (ns)
 #ifndef RLE_SLEEP_A
-#define RLE_SLEEP_A 100
-#endif
-#ifndef RLE_SLEEP_B
-#define RLE_SLEEP_B 200
+#define RLE_SLEEP_A 200
 #endif
 #ifndef RLE_PF_LEAD
-#define RLE_PF_LEAD 1024  // tiles between a load and the L2 prefetch issued with it (0: none)
+#define RLE_PF_LEAD 0  // tiles between a load and an L2 prefetch issued with it (0: none; measured: no gain with two buffers)
 #endif
 #ifndef RLE_CTAS
 #define RLE_CTAS 4
@@ -76,7 +76,6 @@ static constexpr int RLE_Q = 32;                        // tiles of one CTA that
 static constexpr int RLE_CTAS_PER_SM = RLE_CTAS;
 static constexpr uint64_t RL_BIAS = 255;                // run starts are stored as S + 255 >= 0
 static constexpr uint32_t BAR_COMPUTE = 1;              // named barrier of the compute warps
-static constexpr int RLE_SMEM = 1024 + RL_NBUF * RL_TILE + 2 * RL_RINGB;  // 1 KiB: the swizzle needs 1024-byte aligned buffers
 static_assert((RL_RING & (RL_RING - 1)) == 0 && RL_RING >= 512, "ring indices are masked");
 static_assert(RL_ROW == 128 && RL_WSPAN == 32 * RL_ROW, "one row per lane, one 32-row box per warp");
 
@@ -112,6 +111,7 @@ __device__ __forceinline__ uint64_t lookback_run_start(const uint64_t* d1, long 
         const unsigned inv = __ballot_sync(0xffffffffu, (v >> 62) == 0);
         const unsigned before = fin ? ((1u << (__ffs(fin) - 1)) - 1u) : 0xffffffffu;  // lanes nearer than the first final one
         if (inv & before) {
+            __nanosleep(RLE_SLEEP_A);
             if ((v >> 62) == 0) v = ld_relaxed_u64(d1 + j);  // only the lanes that saw nothing re-poll
             continue;
         }
@@ -198,16 +198,15 @@ struct RlePending {               // a tile of this CTA, from "taken" to "stored
     uint32_t total;                // staged pairs that are emitted (start before n)
     uint32_t total_all;            // staged pair boundaries (after the tile's first run start), emitted or not
     uint32_t first_byte;           // in[tile base]: the value of the run that enters the tile
-    // written by the service warp
     long long tile;
+    uint64_t g0;                   // first pair slot of the tile (the scanner's answer)
+    // written by the service warp BEFORE it posts the tile's pair count: whoever sees the scanner's answer sees these
     uint32_t tot;                  // pairs of the tile (staged + nl)
     uint32_t nl;                   // emitted pairs that start at 255-splits before the tile's first run start
     uint32_t nl_all;               // the same splits, emitted or not
     uint32_t lead_first;           // tile-relative position of the first such split
     uint32_t first_start;          // tile-relative position of the tile's first run start (RL_TILE if none)
     uint32_t lagged;               // count of the last pair before the tile; 0 = not ours to write
-    // written by the base warp
-    uint64_t g0;                   // first pair slot of the tile
 };
 
 struct RleMeta {                   // compute warps -> service warp, per tile
@@ -222,19 +221,53 @@ struct RleShared {
     __align__(16) int wfirst[2][RL_WARPS];     // first run start in the warp's 4 KiB (tile relative), RL_TILE if none
     __align__(16) int wlast[2][RL_WARPS];      // last run start, -1 if none
     __align__(16) uint32_t wcnt[2][RL_WARPS];  // boundaries found by the warp's rows: all | those before n << 16
-    uint32_t store_upto[2];        // compute warps' common snapshot of n_ready
+    __align__(16) uint8_t prev16[RL_NBUF][16]; // the 16 bytes before the tile (tile 0: unused)
+    uint32_t store_upto[2];        // tiles of this CTA whose first slot is known (snapshot shared by the compute warps)
     RleMeta meta[2];
     long long cur_tile[RL_NBUF];   // service warp -> compute warps (-1: no more tiles)
-    uint32_t prev_byte[RL_NBUF];   // the byte before the tile
-    uint32_t n_meta;               // service warp -> base warp: tiles whose pair count is posted
-    uint32_t n_ready;              // base warp -> compute warps: tiles whose first slot is known
-    uint32_t done;                 // service warp -> base warp: no more tiles
     uint32_t role;                 // 0: this CTA is the grid's scanner
     RlePending q[RLE_Q];
 };
 
-__device__ __forceinline__ uint32_t ld_volatile_shared(const uint32_t* p) { return *reinterpret_cast<const volatile uint32_t*>(p); }
-__device__ __forceinline__ void st_volatile_shared(uint32_t* p, uint32_t v) { *reinterpret_cast<volatile uint32_t*>(p) = v; }
+// dynamic shared memory: [pad to 1 KiB][RL_NBUF swizzled tile buffers][ring of values][ring of positions][RleShared]
+static constexpr int RLE_SMEM = 1024 + RL_NBUF * RL_TILE + 2 * RL_RINGB + (int)sizeof(RleShared);
+__device__ __forceinline__ uint8_t* rle_smem()
+{
+    extern __shared__ uint8_t smem_raw[];
+    return smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+}
+__device__ __forceinline__ uint8_t* rle_val8() { return rle_smem() + RL_NBUF * RL_TILE; }
+__device__ __forceinline__ uint8_t* rle_pos8() { return rle_val8() + RL_RINGB; }
+__device__ __forceinline__ RleShared& rle_shared() { return *reinterpret_cast<RleShared*>(rle_pos8() + RL_RINGB); }
+
+// Writes a tile whose first slot is known (compute threads, all of them): the count the previous tile left to this one,
+// the pairs at 255-splits before its first run start (long runs only), then its staged pairs.  The tile's last count is
+// left to the next tile (it knows where the next boundary is) unless a boundary past n is staged behind it.
+// One copy of this code in the kernel: the tile loop has to stay small (instruction cache).
+__device__ __noinline__ void rle_store_tile(uint32_t qi, uint8_t* __restrict__ counts, uint8_t* __restrict__ values, size_t pair_cap,
+                                            uint64_t* __restrict__ d_pairs, long long tiles, int tid)
+{
+    const RlePending& e = rle_shared().q[qi];
+    const uint32_t nl = e.nl;
+    const uint64_t g0 = e.g0;
+    if (tid == 0) {
+        if (e.lagged && g0 >= 1 && g0 - 1 < pair_cap) counts[g0 - 1] = (uint8_t)e.lagged;
+        if (e.tile == tiles - 1) *d_pairs = g0 + e.tot;
+    }
+    const bool lead_lag = e.nl_all == nl && e.total_all == 0;  // the last split is the tile's last boundary
+    for (uint32_t j = tid; j < nl; j += RL_THREADS) {
+        const uint32_t p = e.lead_first + 255u * j;
+        const uint64_t kk = g0 + j;
+        if (kk < pair_cap) {
+            values[kk] = (uint8_t)e.first_byte;
+            if (!(j == nl - 1 && lead_lag)) counts[kk] = (uint8_t)min(255u, e.first_start - p);
+        }
+    }
+    if (e.total) {
+        store_from_ring<false>(values, g0 + nl, e.total, pair_cap, rle_val8(), e.head, tid);
+        store_from_ring<true>(counts, g0 + nl, e.total_all > e.total ? e.total : e.total - 1u, pair_cap, rle_pos8(), e.head, tid);
+    }
+}
 
 __global__ void __launch_bounds__(RLE_THREADS, RLE_CTAS_PER_SM)
 rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_t n_scan,
@@ -242,29 +275,25 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                  uint64_t* __restrict__ d_pairs, uint64_t* __restrict__ d1, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg,
                  uint32_t* __restrict__ next_tile, uint32_t* __restrict__ role, long long tiles)
 {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* const inb = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // two swizzled tile buffers
-    uint8_t* const val8 = inb + RL_NBUF * RL_TILE;     // ring of staged values
-    uint8_t* const pos8 = val8 + RL_RINGB;             // ring of staged positions (mod 256)
+    uint8_t* const inb = rle_smem();                   // swizzled tile buffers
+    uint8_t* const val8 = rle_val8();                  // ring of staged values
+    uint8_t* const pos8 = rle_pos8();                  // ring of staged positions (mod 256)
+    RleShared& sh = rle_shared();
     __shared__ __align__(8) uint64_t full[RL_NBUF][RL_WARPS], freeb[RL_NBUF], meta_bar[2], aux;
-    __shared__ RleShared sh;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) {
         sh.role = atomicAdd(role, 1u);
 #pragma unroll
-        for (int b = 0; b < RL_NBUF; ++b)
+        for (int b = 0; b < RL_NBUF; ++b) {
 #pragma unroll
             for (int s = 0; s < RL_WARPS; ++s) mbar_init(&full[b][s], 1);
-        mbar_init(&freeb[0], RL_WARPS);
-        mbar_init(&freeb[1], RL_WARPS);
+            mbar_init(&freeb[b], RL_WARPS);
+        }
         mbar_init(&meta_bar[0], 1);
         mbar_init(&meta_bar[1], 1);
         mbar_init(&aux, 1);
         fence_mbar_init();
-        sh.n_meta = 0;
-        sh.n_ready = 0;
-        sh.done = 0;
     }
     __syncthreads();
     if (sh.role == 0) {  // the first CTA that runs is the scanner
@@ -277,16 +306,14 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         const long long rows_full = (long long)(n_avail / RL_ROW);  // rows the tensor map covers
         const uint32_t tail_bytes = (uint32_t)(n_avail % RL_ROW);   // bytes of the partial row behind them (plain loads)
         uint32_t aux_par = 0;
-        // takes the next tile id and starts its loads into buffer b; returns the id
-        auto start_tile = [&](int b) -> long long {
-            long long tile = 0;
-            if (lane == 0) tile = atomicAdd(next_tile, 1u);
-            tile = __shfl_sync(0xffffffffu, tile, 0);
+        // starts the loads of tile `tile` into buffer b (tile >= tiles: the end marker).  Nothing here waits for
+        // global memory: the 16 bytes before the tile come by bulk copy on the first box's mbarrier.
+        auto start_tile = [&](long long tile, int b) {
             if (tile >= tiles) {
                 if (lane == 0) sh.cur_tile[b] = -1;
                 __syncwarp();
                 if (lane < RL_WARPS) mbar_arrive(&full[b][lane]);
-                return tile;
+                return;
             }
             uint8_t* const buf = inb + b * RL_TILE;
             const size_t tbase = (size_t)tile * RL_TILE;
@@ -304,11 +331,15 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                         tma_load_rows(buf + lane * RL_WSPAN, &tmap, (int)(row0 + 32 * lane), &aux);
                     }
                 } else if (have) {
-                    if (lane == 0) mbar_expect_tx_only(&full[b][0], RL_WSPAN);  // lane 0 arrives below, with the byte before the tile
+                    if (lane == 0) mbar_expect_tx_only(&full[b][0], RL_WSPAN);  // lane 0 arrives below
                     else mbar_expect_tx(&full[b][lane], RL_WSPAN);
                     tma_load_rows(buf + lane * RL_WSPAN, &tmap, (int)(row0 + 32 * lane), &full[b][lane]);
                 } else if (lane != 0) {
                     mbar_arrive(&full[b][lane]);
+                }
+                if (lane == 0 && tile > 0) {  // the 16 bytes before the tile (its last byte is what the first row needs)
+                    mbar_expect_tx_only(&full[b][0], 16);
+                    tma_load_1d(sh.prev16[b], in + tbase - 16, 16, &full[b][0]);
                 }
 #if RLE_PF_LEAD
                 // make the load of the tile one grid of tiles ahead an L2 hit (somebody else's tile)
@@ -329,26 +360,33 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                 __syncwarp();
                 if (lane == 0 && tail_part != 0) mbar_arrive(&full[b][tail_part]);
             }
-            if (lane == 0) {
-                // the byte before the tile; "before" the stream: a byte that differs from in[0] unless a run is open
-                sh.prev_byte[b] = tile > 0 ? in[tbase - 1] : (has_prev ? in[0] : (uint8_t)~in[0]);
-                mbar_arrive(&full[b][0]);
-            }
-            return tile;
+            if (lane == 0) mbar_arrive(&full[b][0]);
         };
-
-        long long cur = start_tile(0);
+        // tile ids are taken one tile ahead of their loads, so the atomic's round trip is never waited for
+        long long cur = 0, nxt = 0, nxt2 = 0;
+        if (lane == 0) {
+            cur = atomicAdd(next_tile, 2u);
+            nxt = cur + 1;
+        }
+        cur = __shfl_sync(0xffffffffu, cur, 0);
+        nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        start_tile(cur, 0);
         for (uint32_t k = 0;; ++k) {
             const long long tile = cur;
             if (tile >= tiles) break;
             const uint32_t kb = k & 1u;
-            if (k) mbar_wait(&freeb[kb ^ 1u], ((k - 1) >> 1) & 1u);  // the compute warps are done with tile k-1: its buffer takes tile k+1
-            const long long nxt = start_tile((int)(kb ^ 1u));
             const size_t tbase = (size_t)tile * RL_TILE;
             const uint32_t rel_emit = n > tbase ? (uint32_t)dmin((size_t)(n - tbase), (size_t)RL_TILE) : 0u;
+            if (lane == 0) nxt2 = atomicAdd(next_tile, 1u);  // id of tile k+2 of this CTA: used at the end of the iteration
+            if (RL_NBUF > 1) {
+                // the next tile's loads go first: a look-back that has to wait must not hold them up (it would delay this
+                // CTA's next tile, whose run start other look-backs wait for in turn)
+                if (k) mbar_wait_sleep(&freeb[(k - 1) % RL_NBUF], ((k - 1) / RL_NBUF) & 1u);  // tile k-1's buffer takes tile k+1
+                start_tile(nxt, (int)((k + 1) % RL_NBUF));
+            }
             uint64_t sbB = prev_phase ? RL_BIAS - prev_phase : 0;   // biased start of the run that enters the tile
             if (tile > 0) sbB = lookback_run_start(d1, tile, lane);
-            mbar_wait(&meta_bar[kb], (k >> 1) & 1u);  // the compute warps have counted the tile
+            mbar_wait_sleep(&meta_bar[kb], (k >> 1) & 1u);  // the compute warps have counted the tile
             const int F_t = sh.meta[kb].first_start;
             const int L_t = sh.meta[kb].last_start;
             const uint32_t total_emit = sh.meta[kb].total_emit;
@@ -364,9 +402,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             const uint32_t lagged = nl_all ? 255u : (uint32_t)(FB - BpB);  // count of the last pair before this tile
             const uint32_t tot = nl + total_emit;
             if (lane == 0) {
-                st_relaxed_u32(agg + tile, 0x80000000u | tot);  // to the scanner
                 RlePending& e = sh.q[k % RLE_Q];
-                e.tile = tile;
                 e.tot = tot;
                 e.nl = nl;
                 e.nl_all = nl_all;
@@ -375,56 +411,16 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                 // the previous tile leaves its last pair's count to us when that pair is the last boundary before this
                 // tile (it cannot know where the next boundary is); a boundary at or past n is not a pair
                 e.lagged = (tile > 0 && BpB < n + RL_BIAS) ? lagged : 0u;
-                __threadfence_block();
-                st_volatile_shared(&sh.n_meta, k + 1);
+                __threadfence_block();  // ... before the post: the scanner's answer implies the six words above
+                st_relaxed_u32(agg + tile, 0x80000000u | tot);  // to the scanner
             }
             __syncwarp();
+            if (RL_NBUF == 1) {
+                mbar_wait_sleep(&freeb[0], k & 1u);  // the compute warps are done with the tile: the buffer takes the next one
+                start_tile(nxt, 0);
+            }
             cur = nxt;
-        }
-        if (lane == 0) {
-            __threadfence_block();
-            st_volatile_shared(&sh.done, 1u);
-        }
-        return;
-    }
-
-    if (warp == RL_WARPS + 1) {
-        // ================================== base warp ============================================
-        // one lane per waiting tile polls the scanner's answer; first slots are handed over in tile order
-        uint32_t n_ready = 0;
-        while (true) {
-            const uint32_t done = ld_volatile_shared(&sh.done);
-            const uint32_t n_meta = ld_volatile_shared(&sh.n_meta);
-            if (n_ready == n_meta) {
-                if (done && n_ready == ld_volatile_shared(&sh.n_meta)) break;
-                __nanosleep(RLE_SLEEP_A);
-                continue;
-            }
-            __threadfence_block();
-            const uint32_t idx = n_ready + lane;
-            const bool have = idx < n_meta;
-            RlePending& e = sh.q[idx % RLE_Q];
-            uint64_t g = 0;
-            if (have) g = e.tile > 0 ? ld_relaxed_u64(inc + e.tile) : (1ull << 63);
-            const unsigned ok = __ballot_sync(0xffffffffu, have && (g >> 63));
-            const uint32_t r = (uint32_t)__ffs(~ok) - 1u;  // leading lanes whose slot is known (ffs(0) = 0 -> all 32)
-            const uint32_t rr = ok == 0xffffffffu ? 32u : r;
-            if (lane < rr) {
-                g &= ~(1ull << 63);
-                e.g0 = g;
-                if (e.lagged && g >= 1 && g - 1 < pair_cap) counts[g - 1] = (uint8_t)e.lagged;
-                if (e.tile == tiles - 1) *d_pairs = g + e.tot;
-            }
-            __syncwarp();
-            if (rr) {
-                n_ready += rr;
-                if (lane == 0) {
-                    __threadfence_block();
-                    st_volatile_shared(&sh.n_ready, n_ready);
-                }
-            } else {
-                __nanosleep(RLE_SLEEP_B);
-            }
+            nxt = __shfl_sync(0xffffffffu, nxt2, 0);
         }
         return;
     }
@@ -436,51 +432,38 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
     uint32_t n_stored = 0;   // tiles of this CTA already written to global memory
     uint32_t ring_head = 0;  // ring position after the last staged boundary (not masked)
 
-    // writes a tile whose first slot is known: the pairs at 255-splits before its first run start (long runs only),
-    // then its staged pairs.  The tile's last count is left to the next tile (it knows where the next boundary is)
-    // unless a boundary past n is staged behind it.
-    auto store_tile = [&](const RlePending& e) {
-        const uint32_t nl = e.nl;
-        const bool lead_lag = e.nl_all == nl && e.total_all == 0;  // the last split is the tile's last boundary
-        for (uint32_t j = tid; j < nl; j += RL_THREADS) {
-            const uint32_t p = e.lead_first + 255u * j;
-            const uint64_t kk = e.g0 + j;
-            if (kk < pair_cap) {
-                values[kk] = (uint8_t)e.first_byte;
-                if (!(j == nl - 1 && lead_lag)) counts[kk] = (uint8_t)min(255u, e.first_start - p);
-            }
-        }
-        if (e.total) {
-            store_from_ring<false>(values, e.g0 + nl, e.total, pair_cap, val8, e.head, tid);
-            store_from_ring<true>(counts, e.g0 + nl, e.total_all > e.total ? e.total : e.total - 1u, pair_cap, pos8, e.head, tid);
-        }
-    };
-    // blocks until the first slots of the CTA's first `need` tiles are known; returns how many are (>= need)
-    auto wait_ready = [&](uint32_t need) -> uint32_t {
-        bar_sync(BAR_COMPUTE, RL_THREADS);  // everybody has read the previous snapshot
+    auto store_tile = [&](uint32_t i) { rle_store_tile(i % RLE_Q, counts, values, pair_cap, d_pairs, tiles, tid); };
+    // blocks until the first slots of this CTA's tiles [n_stored, need) are known (the scanner has answered them)
+    auto wait_slots = [&](uint32_t need) {
         if (tid == 0) {
-            uint32_t r;
-            while ((r = ld_volatile_shared(&sh.n_ready)) < need) __nanosleep(RLE_SLEEP_A);
-            __threadfence_block();
-            sh.store_upto[0] = r;
+            for (uint32_t i = n_stored; i < need; ++i) {
+                uint64_t g;
+                while (!((g = ld_relaxed_u64(inc + sh.q[i % RLE_Q].tile)) >> 63)) __nanosleep(RLE_SLEEP_A);
+                sh.q[i % RLE_Q].g0 = g & ~(1ull << 63);
+            }
+            __threadfence_block();  // the answer follows the service warp's post, which follows its part of the entry
         }
         bar_sync(BAR_COMPUTE, RL_THREADS);
-        const uint32_t r = sh.store_upto[0];
-        bar_sync(BAR_COMPUTE, RL_THREADS);  // ... before the slot is reused
-        return r;
     };
 
-    for (uint32_t k = 0;; ++k) {
-        const uint32_t kb = k & 1u, fpar = (k >> 1) & 1u;
+    uint32_t k = 0;  // tiles of this CTA that have been staged
+    for (;; ++k) {
+        const uint32_t kb = k & 1u, buf_i = k % RL_NBUF, fpar = (k / RL_NBUF) & 1u;
         if (k - n_stored >= (uint32_t)RLE_Q - 1u) {  // the queue of waiting tiles is full (rare)
-            const uint32_t upto = wait_ready(n_stored + 1u);
-            for (; n_stored < upto; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
+            wait_slots(n_stored + 1u);
+            store_tile(n_stored++);
         }
-        if (warp > 0) mbar_wait(&full[kb][warp - 1], fpar);  // the last byte of the previous warp's rows
-        mbar_wait(&full[kb][warp], fpar);
-        const long long tile = *reinterpret_cast<const volatile long long*>(&sh.cur_tile[kb]);
+        // ask for the first slots of the two oldest waiting tiles: the answers arrive while the masks are computed
+        uint64_t ga = 0, gb = 0;
+        if (tid == 0) {
+            if (n_stored < k) ga = ld_relaxed_u64(inc + sh.q[n_stored % RLE_Q].tile);
+            if (n_stored + 1u < k) gb = ld_relaxed_u64(inc + sh.q[(n_stored + 1u) % RLE_Q].tile);
+        }
+        if (warp > 0) mbar_wait(&full[buf_i][warp - 1], fpar);  // the last byte of the previous warp's rows
+        mbar_wait(&full[buf_i][warp], fpar);
+        const long long tile = *reinterpret_cast<const volatile long long*>(&sh.cur_tile[buf_i]);
         if (tile < 0) break;
-        const uint8_t* const buf = inb + kb * RL_TILE;
+        const uint8_t* const buf = inb + buf_i * RL_TILE;
         const uint8_t* const rowp = buf + rowstart;
         const size_t tbase = (size_t)tile * RL_TILE;
         // tile-relative limits: positions >= rel_emit are not emitted; position rel_scan is a forced boundary (the end
@@ -493,8 +476,10 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         uint32_t M[4];
         {
             // the word that ends with the byte before the row (only its top byte is used)
-            uint32_t pw = tid == 0 ? ld_volatile_shared(&sh.prev_byte[kb]) << 24
-                                   : *reinterpret_cast<const uint32_t*>(buf + (rowstart - RL_ROW) + (((7u ^ (uint32_t)(tid - 1)) & 7u) << 4) + 12);
+            // ("before" the stream: a byte that differs from in[0] unless a run is open)
+            uint32_t pw = tid > 0    ? *reinterpret_cast<const uint32_t*>(buf + (rowstart - RL_ROW) + (((7u ^ (uint32_t)(tid - 1)) & 7u) << 4) + 12)
+                          : tile > 0 ? *reinterpret_cast<const volatile uint32_t*>(&sh.prev16[buf_i][12])
+                                     : (uint32_t)(has_prev ? buf[0] : (uint8_t)~buf[0]) << 24;
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
                 const uint4 a = *reinterpret_cast<const uint4*>(rowp + (((2u * g) ^ sw) << 4));
@@ -515,8 +500,9 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         const uint32_t any = M[0] | M[1] | M[2] | M[3];
         const unsigned bal = __ballot_sync(0xffffffffu, any != 0);
         // bytes of the row that continue the entering run / last run start of the row (tile relative)
-        const int lead = M[0] ? __ffs(M[0]) - 1 : M[1] ? 31 + __ffs(M[1]) : M[2] ? 63 + __ffs(M[2]) : M[3] ? 95 + __ffs(M[3]) : RL_ROW;
-        const int my_last = rowstart + (M[3] ? 127 - __clz(M[3]) : M[2] ? 95 - __clz(M[2]) : M[1] ? 63 - __clz(M[1]) : 31 - __clz(M[0]));
+        const unsigned long long mlo = (unsigned long long)M[0] | ((unsigned long long)M[1] << 32), mhi = (unsigned long long)M[2] | ((unsigned long long)M[3] << 32);
+        const int lead = mlo ? __ffsll((long long)mlo) - 1 : mhi ? 63 + __ffsll((long long)mhi) : RL_ROW;
+        const int my_last = rowstart + (mhi ? 127 - __clzll((long long)mhi) : 63 - __clzll((long long)mlo));
         const unsigned lower = bal & lt_mask;
         const int S = __shfl_sync(0xffffffffu, my_last, 31 - __clz(lower | 1u));  // nearest run start before the row, if lower != 0
         if (lower != 0 && (rowstart - S) + lead > 255 && !(ragged && rowstart > (int)rel_scan)) {
@@ -562,8 +548,12 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             sh.wlast[kb][warp] = -1;
         }
         if (tid == 0) {  // which of the waiting tiles can be written after this tile's compaction
-            const uint32_t r = ld_volatile_shared(&sh.n_ready);
-            __threadfence_block();
+            uint32_t r = n_stored;
+            if (ga >> 63) {
+                sh.q[r++ % RLE_Q].g0 = ga & ~(1ull << 63);
+                if (gb >> 63) sh.q[r++ % RLE_Q].g0 = gb & ~(1ull << 63);
+                __threadfence_block();  // the answer follows the service warp's post, which follows its part of the entry
+            }
             sh.store_upto[kb] = r;
         }
         bar_sync(BAR_COMPUTE, RL_THREADS);
@@ -623,6 +613,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             mbar_arrive(&meta_bar[kb]);  // release: the service warp reads the four words above
             me.total_all = total_all;
             me.first_byte = buf[0];
+            me.tile = tile;
         }
 
         // ---- compaction: value and position of every boundary into the ring
@@ -631,9 +622,10 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             // room in the ring?  (the oldest waiting tile's boundaries start at its `head`)
             if (n_stored < k && ring_head + total_all - sh.q[n_stored % RLE_Q].head > (uint32_t)RL_RING) {
                 do {
-                    upto = wait_ready(n_stored + 1u);
-                    for (; n_stored < upto && n_stored < k; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
+                    if (n_stored >= upto) wait_slots(n_stored + 1u);
+                    store_tile(n_stored++);
                 } while (n_stored < k && ring_head + total_all - sh.q[n_stored % RLE_Q].head > (uint32_t)RL_RING);
+                if (upto < n_stored) upto = n_stored;
                 bar_sync(BAR_COMPUTE, RL_THREADS);  // every warp has read the ring space that is written next
             }
             const uint32_t wb = ring_head + mybase;
@@ -666,17 +658,18 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             }
             ring_head += total_all;
             __syncwarp();
-            if (lane == 0) mbar_arrive(&freeb[kb]);  // the tile buffer may be refilled
-            for (; n_stored < upto && n_stored < k; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
+            if (lane == 0) mbar_arrive(&freeb[buf_i]);  // the tile buffer may be refilled
+            while (n_stored < upto) store_tile(n_stored++);
         } else {
             // rare: more boundaries than the ring holds -> written at once, in rounds, after everything that waits
             if (tid == 0) {
                 me.head = 0;
                 me.total = 0;
             }
-            upto = wait_ready(k + 1u);
-            for (; n_stored < k; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
-            store_tile(me);  // its pairs at 255-splits before the first run start
+            bar_sync(BAR_COMPUTE, RL_THREADS);  // me.* is written
+            wait_slots(k + 1u);
+            while (n_stored < k) store_tile(n_stored++);
+            store_tile(k);  // its pairs at 255-splits before the first run start
             const uint64_t g0 = me.g0 + me.nl;
             const uint32_t rel0 = mybase + mynl + excl;  // tile-relative index of the row's first boundary
             for (uint32_t w0 = 0; w0 < total_emit; w0 += RL_RING) {
@@ -712,15 +705,17 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             n_stored = k + 1u;
             bar_sync(BAR_COMPUTE, RL_THREADS);  // the ring has been read
             ring_head = 0;
-            if (lane == 0) mbar_arrive(&freeb[kb]);
+            if (lane == 0) mbar_arrive(&freeb[buf_i]);
         }
     }
     // ---- the tiles that still wait
     {
-        const uint32_t k_end = ld_volatile_shared(&sh.n_meta);  // == tiles taken by this CTA (every one of them was counted)
+        // the service warp may still be posting the last of them (it starts the next load, here the end marker, first)
+        const uint32_t k_end = k;
         if (n_stored < k_end) {
-            wait_ready(k_end);
-            for (; n_stored < k_end; ++n_stored) store_tile(sh.q[n_stored % RLE_Q]);
+            bar_sync(BAR_COMPUTE, RL_THREADS);
+            wait_slots(k_end);
+            while (n_stored < k_end) store_tile(n_stored++);
         }
     }
 }
