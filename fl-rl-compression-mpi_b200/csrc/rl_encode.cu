@@ -145,7 +145,7 @@ __device__ __forceinline__ uint4 lds_diff16(const uint8_t* buf, uint32_t u)
 // two positions), else stage[soff + i] (a value).
 template <bool DIFF>
 __device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint64_t g0, uint32_t cnt, uint64_t cap,
-                                                const uint8_t* stage, uint32_t soff, int tid)
+                                                const uint8_t* stage, uint32_t soff, int tid, int nthr = RL_THREADS)
 {
     if (cap <= g0) return;
     if (cap - g0 < cnt) cnt = (uint32_t)(cap - g0);
@@ -153,7 +153,7 @@ __device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint6
     const uint32_t head = min(cnt, (16u - a) & 15u);        // bytes before the first aligned chunk
     const uint32_t nfull = (cnt - head) >> 4;               // aligned 16-byte chunks
     const uint32_t tail0 = head + 16u * nfull;              // staging index of the first byte after them
-    for (uint32_t q = tid; q < nfull; q += RL_THREADS)
+    for (uint32_t q = tid; q < nfull; q += nthr)
         *reinterpret_cast<uint4*>(dst + g0 + head + 16u * q) =
             DIFF ? lds_diff16(stage, soff + head + 16u * q) : lds_unaligned16(stage, soff + head + 16u * q);
     if ((uint32_t)tid < head) dst[g0 + tid] = DIFF ? (uint8_t)(stage[soff + tid + 1] - stage[soff + tid]) : stage[soff + tid];
@@ -164,12 +164,12 @@ __device__ __forceinline__ void store_compacted(uint8_t* __restrict__ dst, uint6
 // the same from a ring of RL_RING bytes: at most two linear pieces (entry RL_RING mirrors entry 0 for the differences)
 template <bool DIFF>
 __device__ __forceinline__ void store_from_ring(uint8_t* __restrict__ dst, uint64_t g0, uint32_t cnt, uint64_t cap,
-                                                const uint8_t* ring, uint32_t head, int tid)
+                                                const uint8_t* ring, uint32_t head, int tid, int nthr)
 {
     const uint32_t h = head & (RL_RING - 1);
     const uint32_t first = min(cnt, (uint32_t)RL_RING - h);
-    store_compacted<DIFF>(dst, g0, first, cap, ring, h, tid);
-    if (cnt > first) store_compacted<DIFF>(dst, g0 + first, cnt - first, cap, ring, 0, tid);
+    store_compacted<DIFF>(dst, g0, first, cap, ring, h, tid, nthr);
+    if (cnt > first) store_compacted<DIFF>(dst, g0 + first, cnt - first, cap, ring, 0, tid, nthr);
 }
 
 template <typename T>
@@ -243,9 +243,11 @@ __device__ __forceinline__ RleShared& rle_shared() { return *reinterpret_cast<Rl
 // Writes a tile whose first slot is known (compute threads, all of them): the count the previous tile left to this one,
 // the pairs at 255-splits before its first run start (long runs only), then its staged pairs.  The tile's last count is
 // left to the next tile (it knows where the next boundary is) unless a boundary past n is staged behind it.
-// One copy of this code in the kernel: the tile loop has to stay small (instruction cache).
+// One copy of this code in the kernel: the tile loop has to stay small (instruction cache).  Called by `nthr` threads
+// numbered tid = 0 .. nthr-1: all compute threads, or one warp for a tile with few pairs (the routine's fixed cost is
+// then paid once, not four times).
 __device__ __noinline__ void rle_store_tile(uint32_t qi, uint8_t* __restrict__ counts, uint8_t* __restrict__ values, size_t pair_cap,
-                                            uint64_t* __restrict__ d_pairs, long long tiles, int tid)
+                                            uint64_t* __restrict__ d_pairs, long long tiles, int tid, int nthr)
 {
     const RlePending& e = rle_shared().q[qi];
     const uint32_t nl = e.nl;
@@ -255,7 +257,7 @@ __device__ __noinline__ void rle_store_tile(uint32_t qi, uint8_t* __restrict__ c
         if (e.tile == tiles - 1) *d_pairs = g0 + e.tot;
     }
     const bool lead_lag = e.nl_all == nl && e.total_all == 0;  // the last split is the tile's last boundary
-    for (uint32_t j = tid; j < nl; j += RL_THREADS) {
+    for (uint32_t j = tid; j < nl; j += nthr) {
         const uint32_t p = e.lead_first + 255u * j;
         const uint64_t kk = g0 + j;
         if (kk < pair_cap) {
@@ -264,8 +266,8 @@ __device__ __noinline__ void rle_store_tile(uint32_t qi, uint8_t* __restrict__ c
         }
     }
     if (e.total) {
-        store_from_ring<false>(values, g0 + nl, e.total, pair_cap, rle_val8(), e.head, tid);
-        store_from_ring<true>(counts, g0 + nl, e.total_all > e.total ? e.total : e.total - 1u, pair_cap, rle_pos8(), e.head, tid);
+        store_from_ring<false>(values, g0 + nl, e.total, pair_cap, rle_val8(), e.head, tid, nthr);
+        store_from_ring<true>(counts, g0 + nl, e.total_all > e.total ? e.total : e.total - 1u, pair_cap, rle_pos8(), e.head, tid, nthr);
     }
 }
 
@@ -362,7 +364,6 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             }
             if (lane == 0) mbar_arrive(&full[b][0]);
         };
-        // tile ids are taken one tile ahead of their loads, so the atomic's round trip is never waited for
         long long cur = 0, nxt = 0, nxt2 = 0;
         if (lane == 0) {
             cur = atomicAdd(next_tile, 2u);
@@ -377,7 +378,6 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             const uint32_t kb = k & 1u;
             const size_t tbase = (size_t)tile * RL_TILE;
             const uint32_t rel_emit = n > tbase ? (uint32_t)dmin((size_t)(n - tbase), (size_t)RL_TILE) : 0u;
-            if (lane == 0) nxt2 = atomicAdd(next_tile, 1u);  // id of tile k+2 of this CTA: used at the end of the iteration
             if (RL_NBUF > 1) {
                 // the next tile's loads go first: a look-back that has to wait must not hold them up (it would delay this
                 // CTA's next tile, whose run start other look-backs wait for in turn)
@@ -415,6 +415,9 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                 st_relaxed_u32(agg + tile, 0x80000000u | tot);  // to the scanner
             }
             __syncwarp();
+            // the id of this CTA's tile k+2, taken as late as possible (tiles should start in id order: a tile's first slot
+            // waits for every earlier tile) yet early enough that the atomic's round trip hides behind the next wait
+            if (lane == 0) nxt2 = atomicAdd(next_tile, 1u);
             if (RL_NBUF == 1) {
                 mbar_wait_sleep(&freeb[0], k & 1u);  // the compute warps are done with the tile: the buffer takes the next one
                 start_tile(nxt, 0);
@@ -432,13 +435,20 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
     uint32_t n_stored = 0;   // tiles of this CTA already written to global memory
     uint32_t ring_head = 0;  // ring position after the last staged boundary (not masked)
 
-    auto store_tile = [&](uint32_t i) { rle_store_tile(i % RLE_Q, counts, values, pair_cap, d_pairs, tiles, tid); };
+    auto store_tile = [&](uint32_t i) { rle_store_tile(i % RLE_Q, counts, values, pair_cap, d_pairs, tiles, tid, RL_THREADS); };
+    // a tile with few pairs is written by ONE warp (they take turns); the others go on.  Safe: the ring space it reads is
+    // not reused before the next tile's barrier, which that warp reaches only after the store.
+    auto store_tile_light = [&](uint32_t i, uint32_t turn) {
+        const RlePending& e = sh.q[i % RLE_Q];
+        if (e.total + e.nl > 1024u) rle_store_tile(i % RLE_Q, counts, values, pair_cap, d_pairs, tiles, tid, RL_THREADS);
+        else if ((uint32_t)warp == ((turn + i) & (RL_WARPS - 1))) rle_store_tile(i % RLE_Q, counts, values, pair_cap, d_pairs, tiles, lane, 32);
+    };
     // blocks until the first slots of this CTA's tiles [n_stored, need) are known (the scanner has answered them)
     auto wait_slots = [&](uint32_t need) {
         if (tid == 0) {
             for (uint32_t i = n_stored; i < need; ++i) {
                 uint64_t g;
-                while (!((g = ld_relaxed_u64(inc + sh.q[i % RLE_Q].tile)) >> 63)) __nanosleep(RLE_SLEEP_A);
+                while (!((g = ld_relaxed_u64(inc + sh.q[i % RLE_Q].tile)) >> 63)) __nanosleep(50);
                 sh.q[i % RLE_Q].g0 = g & ~(1ull << 63);
             }
             __threadfence_block();  // the answer follows the service warp's post, which follows its part of the entry
@@ -659,7 +669,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             ring_head += total_all;
             __syncwarp();
             if (lane == 0) mbar_arrive(&freeb[buf_i]);  // the tile buffer may be refilled
-            while (n_stored < upto) store_tile(n_stored++);
+            while (n_stored < upto) store_tile_light(n_stored++, k);
         } else {
             // rare: more boundaries than the ring holds -> written at once, in rounds, after everything that waits
             if (tid == 0) {

@@ -2,9 +2,9 @@
 TAG=${1:-x}
 O=gpurun_out/$TAG; mkdir -p $O
 timeout 900 python -m pytest tests/test_rl_gpu.py -x -q -m gpu > $O/pytest_rl.log 2>&1; echo "pytest rc=$?" >> $O/pytest_rl.log; tail -5 $O/pytest_rl.log
-timeout 300 python tools/quick_rl.py > $O/quick_rl.log 2>&1; echo "rc=$?" >> $O/quick_rl.log; cat $O/quick_rl.log
+timeout 300 python tools/quick_rl.py 1073741824 $MEANS > $O/quick_rl.log 2>&1; echo "rc=$?" >> $O/quick_rl.log; cat $O/quick_rl.log
 for V in $VARIANTS; do
-  FLRL_LIB_PATH=$PWD/fl-rl-compression-mpi_b200/variants/libflrl_$V.so timeout 300 python tools/quick_rl.py > $O/quick_rl_$V.log 2>&1; cat $O/quick_rl_$V.log
+  FLRL_LIB_PATH=$PWD/fl-rl-compression-mpi_b200/variants/libflrl_$V.so timeout 300 python tools/quick_rl.py 1073741824 $MEANS > $O/quick_rl_$V.log 2>&1; cat $O/quick_rl_$V.log
 done
 if [ -n "$NCU" ]; then
 B="python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline"
