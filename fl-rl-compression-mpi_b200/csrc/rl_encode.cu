@@ -364,14 +364,15 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             }
             if (lane == 0) mbar_arrive(&full[b][0]);
         };
+        // One id per atomic, also at the start: a CTA that held two CONSECUTIVE ids would make the next CTA's tile wait
+        // (for its first slot) until this CTA has finished a whole tile and counted the second one, and so on down the
+        // grid — measured: tiles with more pairs than the ring holds then run one after the other (170 ms per GiB).
         long long cur = 0, nxt = 0, nxt2 = 0;
-        if (lane == 0) {
-            cur = atomicAdd(next_tile, 2u);
-            nxt = cur + 1;
-        }
+        if (lane == 0) cur = atomicAdd(next_tile, 1u);
         cur = __shfl_sync(0xffffffffu, cur, 0);
-        nxt = __shfl_sync(0xffffffffu, nxt, 0);
         start_tile(cur, 0);
+        if (lane == 0) nxt = atomicAdd(next_tile, 1u);
+        nxt = __shfl_sync(0xffffffffu, nxt, 0);
         for (uint32_t k = 0;; ++k) {
             const long long tile = cur;
             if (tile >= tiles) break;

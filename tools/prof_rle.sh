@@ -13,3 +13,6 @@ for w in $NCU; do
 done
 fi
 ls -la $O
+if [ -n "$NCU1" ]; then
+  timeout 300 ncu --set full --clock-control none --import-source on -k regex:'rl_encode' -s 3 -c 1 -o $O/full_mean1 python tools/quick_rl.py 268435456 1 > $O/ncu_mean1.log 2>&1; tail -3 $O/ncu_mean1.log
+fi
