@@ -230,6 +230,10 @@ lib.flrl_host_free.argtypes = [_vp]
 lib.flrl_free.argtypes = [_vp]
 lib.flrl_last_timing.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
 lib.flrl_set_concat_mode.argtypes = [C.c_int]
+lib.flrl_set_pipe_chunk.argtypes = [_sz]
+lib.flrl_last_gpu_count.restype = C.c_int
+lib.flrl_last_timing_gpu.restype = C.c_int
+lib.flrl_last_timing_gpu.argtypes = [C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
 lib.flrl_fl_gpu_compress_into.restype = C.c_int
 lib.flrl_fl_gpu_compress_into.argtypes = [_vp, _sz, C.c_int, _vp, _sz, _vp, _sz, _szp, _szp]
 lib.flrl_fl_gpu_decompress_into.restype = C.c_int
@@ -397,3 +401,12 @@ class HostCodec:
         k, t = C.c_float(), C.c_float()
         lib.flrl_last_timing(C.byref(k), C.byref(t))
         return k.value, t.value
+
+    def timing_per_gpu(self):
+        """[(kernel_ms, total_ms, h2d_bytes, d2h_bytes)] for every GPU of the last call."""
+        res = []
+        for g in range(lib.flrl_last_gpu_count()):
+            k, t, bi, bo = C.c_float(), C.c_float(), C.c_uint64(), C.c_uint64()
+            _check(lib.flrl_last_timing_gpu(g, C.byref(k), C.byref(t), C.byref(bi), C.byref(bo)), "flrl_last_timing_gpu")
+            res.append((k.value, t.value, bi.value, bo.value))
+        return res

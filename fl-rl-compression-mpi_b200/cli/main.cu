@@ -42,6 +42,20 @@ void printDeviceTimers(const char* what, size_t bytes)
     snprintf(step, sizeof step, "%s (kernels + transfers)", what);
     Timers::printDeviceResult(step, total_ms);
     Timers::printTransfer(what, (double)bytes, total_ms);
+    // one line pair per GPU, as the reference prints per rank (src/timers/cpu_timer_with_transfer.cu:16-40): the time of
+    // that GPU's shard and the rate at which it moved its bytes over PCIe (both directions)
+    const int gpus = flrl_last_gpu_count();
+    for (int g = 0; gpus > 1 && g < gpus; ++g) {
+        float k = 0, t = 0;
+        uint64_t in = 0, out = 0;
+        if (flrl_last_timing_gpu(g, &k, &t, &in, &out) != FLRL_OK) break;
+        snprintf(step, sizeof step, "%s GPU %d (kernels)", what, g);
+        Timers::printDeviceResult(step, k);
+        snprintf(step, sizeof step, "%s GPU %d (kernels + transfers)", what, g);
+        Timers::printDeviceResult(step, t);
+        snprintf(step, sizeof step, "%s GPU %d host<->device", what, g);
+        Timers::printTransfer(step, (double)(in + out), t);
+    }
 }
 
 void compress(Method method, const char* input, const char* output)

@@ -327,7 +327,7 @@ cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_
         if (e != cudaSuccess) return e;
         if (dev < 64) sm_count[dev] = sms;
     }
-    static const int per_sm = getenv("FLRL_FLD_CTAS") ? atoi(getenv("FLRL_FLD_CTAS")) : FLD_CTAS_PER_SM;
+    const int per_sm = FLD_CTAS_PER_SM;
     const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)sms * per_sm);
     uint64_t* desc = reinterpret_cast<uint64_t*>(d_ws);
     int* err = reinterpret_cast<int*>(desc + tiles);

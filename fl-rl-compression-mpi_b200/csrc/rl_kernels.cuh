@@ -20,4 +20,8 @@ const int* rl_decode_status(const void* d_ws, size_t pairs);
 // *d_sum = sum of the n bytes at d_p (16-byte aligned)
 cudaError_t sum_bytes_launch(const uint8_t* d_p, size_t n, uint64_t* d_sum, cudaStream_t stream);
 
+// d_sums[i] = sum of d_p[i*seg .. min((i+1)*seg, n)) for i < nseg = ceil(n / seg); d_sums[nseg] = 1 if a byte is 0, | 2 if a
+// byte is > 8 (FL widths must be 1..8, RL counts >= 1).  d_p 16-byte aligned, seg a multiple of 16; d_sums holds nseg + 1 words.
+cudaError_t segment_sums_launch(const uint8_t* d_p, size_t n, size_t seg, uint64_t* d_sums, cudaStream_t stream);
+
 }  // namespace flrl

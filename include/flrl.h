@@ -158,8 +158,12 @@ int flrl_rl_gpu_decompress_into(const uint8_t* counts, const uint8_t* values, si
  * 1: every GPU peer-copies (cudaMemcpyPeerAsync over NVLink) into GPU 0's buffer, which is then copied to the
  *    host once — the device-resident merge of gpuNCCLCompress (fl_gpu.cu:221-238, :280). */
 void flrl_set_concat_mode(int peer);
-/* Frees the per-device caches (buffers, streams, pinned staging) the host layer keeps between calls. */
+/* Frees the per-device caches (buffers, streams, events, pinned staging, the chunk pipeline's too) the host layer keeps
+ * between calls. */
 void flrl_release(void);
+/* Chunk size of the host layer's copy / kernel / copy pipeline (default 64 MiB; 0 restores it; rounded to 4 KiB, at
+ * least 64 KiB).  A test hook: outputs do not depend on it. */
+void flrl_set_pipe_chunk(size_t bytes);
 
 /* CPU methods of the CLI (`fl-cpu`, `rl-cpu`): FixedLength::cpuCompress / cpuDecompress
  * (fl_cpu.cu:9-147) and the RL spec.  These ARE CPU methods by definition; the GPU entry
@@ -179,6 +183,10 @@ void flrl_host_free(void* p);
 /* Device timing of the last host-layer call on this thread (cudaEvent, ms): kernels only,
  * and whole call including copies.  Mirrors the reference's GpuTimer (src/timers/gpu_timer.cu). */
 void flrl_last_timing(float* kernel_ms, float* total_ms);
+/* The same per GPU of the last call (g = 0 .. flrl_last_gpu_count() - 1), with the bytes that GPU moved over PCIe
+ * (host -> device, device -> host): the reference's per-rank transfer lines (src/timers/cpu_timer_with_transfer.cu:16-40). */
+int flrl_last_gpu_count(void);
+int flrl_last_timing_gpu(int g, float* kernel_ms, float* total_ms, uint64_t* bytes_in, uint64_t* bytes_out);
 
 #ifdef __cplusplus
 }

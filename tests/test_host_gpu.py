@@ -62,23 +62,81 @@ def test_host_pinned_round_trip(kind, oracle, flrl):
 
 
 @pytest.mark.parametrize("kind,mean", [("fl", 0), ("rl", 40), ("rl", 3), ("rl", 3_000_000)])
-def test_host_chunk_pipeline(kind, mean, oracle, flrl, monkeypatch):
+def test_host_chunk_pipeline(kind, mean, oracle, flrl):
     """The single-GPU chunk pipeline (copy-in / kernel / copy-out overlapped, pinned buffers) with small chunks: chunk
     outputs must concatenate to the single-stream output (FL: 128-aligned chunks; RL: prev_run + look-ahead, runs
     longer than a chunk carried over whole chunks)."""
-    monkeypatch.setenv("FLRL_PIPE_CHUNK", str(1 << 20))
-    n = (11 << 20) + 128 * 5 + 77
-    data = make_fl_mix(n, seed=5) if kind == "fl" else _rl_data(n, mean, 6)
-    hc = flrl.HostCodec(kind, n, ngpus=1)
-    hc.load_input(data)
-    hc.compress()
-    meta, payload = hc.compressed()
-    m_ref, p_ref = (oracle.fl_compress if kind == "fl" else oracle.rl_compress)(data)
-    assert np.array_equal(meta, m_ref) and np.array_equal(payload, p_ref), kind
-    hc.decompress()
-    assert hc.check_round_trip(), kind
-    k_ms, t_ms = hc.timing()
-    assert 0 < k_ms <= t_ms
+    flrl.lib.flrl_set_pipe_chunk(1 << 20)
+    try:
+        n = (11 << 20) + 128 * 5 + 77
+        data = make_fl_mix(n, seed=5) if kind == "fl" else _rl_data(n, mean, 6)
+        m_ref, p_ref = (oracle.fl_compress if kind == "fl" else oracle.rl_compress)(data)
+        for g in _ngpus():  # every shard runs its own pipeline; shard 0 delivers as it goes, the others after the size exchange
+            for peer in ((0, 1) if g > 1 else (0,)):
+                flrl.lib.flrl_set_concat_mode(peer)
+                hc = flrl.HostCodec(kind, n, ngpus=g)
+                hc.load_input(data)
+                hc.compress()
+                meta, payload = hc.compressed()
+                assert np.array_equal(meta, m_ref) and np.array_equal(payload, p_ref), (kind, g, peer)
+                hc.decompress()
+                assert hc.check_round_trip(), (kind, g, peer)
+                k_ms, t_ms = hc.timing()
+                assert 0 < k_ms <= t_ms
+                per = hc.timing_per_gpu()
+                assert len(per) == g and all(t > 0 and bi > 0 and bo > 0 for _, t, bi, bo in per)
+    finally:
+        flrl.lib.flrl_set_pipe_chunk(0)
+        flrl.lib.flrl_set_concat_mode(0)
+
+
+def test_host_pipeline_rejects_malformed(oracle, flrl):
+    """A container whose widths are out of range must be refused before any chunk is copied: a width of 255 would make
+    a chunk's value bytes exceed the pipeline's staging buffer (pinned buffers, several chunks)."""
+    flrl.lib.flrl_set_pipe_chunk(1 << 20)
+    try:
+        n = (5 << 20) + 300
+        data = make_fl_mix(n, seed=11)
+        hc = flrl.HostCodec("fl", n, ngpus=1)
+        hc.load_input(data)
+        hc.compress()
+        meta, payload = hc.compressed()
+        meta[12345] = 255
+        with pytest.raises(flrl.FlrlError):
+            hc.decompress()
+        meta[12345] = 0
+        with pytest.raises(flrl.FlrlError):
+            hc.decompress()
+        hc.compress()
+        hc.s1.value -= 4096  # values shorter than the widths imply
+        with pytest.raises(flrl.FlrlError):
+            hc.decompress()
+        rc = flrl.HostCodec("rl", n, ngpus=1)
+        rc.load_input(_rl_data(n, 5, 12))
+        rc.compress()
+        counts, _ = rc.compressed()
+        counts[777] = 0
+        with pytest.raises(flrl.FlrlError):
+            rc.decompress()
+    finally:
+        flrl.lib.flrl_set_pipe_chunk(0)
+
+
+def test_host_release_and_reuse(oracle, flrl):
+    """flrl_release() frees every cached buffer, stream and event (the pipeline's too); the next call rebuilds them."""
+    n = (3 << 20) + 5
+    data = make_fl_mix(n, seed=13)
+    flrl.lib.flrl_set_pipe_chunk(1 << 20)
+    try:
+        hc = flrl.HostCodec("fl", n, ngpus=1)
+        hc.load_input(data)
+        hc.compress()
+        flrl.lib.flrl_release()
+        hc.compress()
+        hc.decompress()
+        assert hc.check_round_trip()
+    finally:
+        flrl.lib.flrl_set_pipe_chunk(0)
 
 
 @pytest.mark.parametrize("peer", [0, 1])

@@ -77,15 +77,22 @@ def test_rl_device_parity(which, oracle, flrl):
 
 
 @pytest.mark.parametrize("kind", ["fl", "rl"])
-def test_host_layer_mixed_stream_chunked(kind, oracle, flrl, monkeypatch):
-    """configs[4] shape through the host layer's chunk pipeline (2 MiB chunks: every segment kind meets a chunk cut)."""
-    monkeypatch.setenv("FLRL_PIPE_CHUNK", str(2 << 20))
-    data = mixed_entropy_stream(11)[: (11 << 20) - 4321]
-    hc = flrl.HostCodec(kind, data.size, ngpus=1)
-    hc.load_input(data)
-    hc.compress()
-    meta, payload = hc.compressed()
-    m_ref, p_ref = (oracle.fl_compress if kind == "fl" else oracle.rl_compress)(data)
-    assert np.array_equal(meta, m_ref) and np.array_equal(payload, p_ref)
-    hc.decompress()
-    assert hc.check_round_trip()
+def test_host_layer_mixed_stream_chunked(kind, oracle, flrl):
+    """configs[4] shape through the host layer's chunk pipeline (2 MiB chunks: every segment kind meets a chunk cut),
+    on one GPU and on every GPU count the box has."""
+    import torch
+
+    flrl.lib.flrl_set_pipe_chunk(2 << 20)
+    try:
+        data = mixed_entropy_stream(11)[: (11 << 20) - 4321]
+        m_ref, p_ref = (oracle.fl_compress if kind == "fl" else oracle.rl_compress)(data)
+        for g in [g for g in (1, 2, 4, 8) if g <= torch.cuda.device_count()]:
+            hc = flrl.HostCodec(kind, data.size, ngpus=g)
+            hc.load_input(data)
+            hc.compress()
+            meta, payload = hc.compressed()
+            assert np.array_equal(meta, m_ref) and np.array_equal(payload, p_ref), g
+            hc.decompress()
+            assert hc.check_round_trip(), g
+    finally:
+        flrl.lib.flrl_set_pipe_chunk(0)
