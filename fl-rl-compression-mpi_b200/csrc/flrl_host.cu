@@ -533,7 +533,9 @@ int deliver(int G, uint8_t* dst, const std::vector<const uint8_t*>& src, const s
             CK(cudaStreamSynchronize(g_dev[g_map[g]].s));
         }
         CK(cudaSetDevice(g_map[0]));
-        return d2h(d0, dst, d0.gather.p, total);
+        if (d2h(d0, dst, d0.gather.p, total)) return -1;
+        CK(cudaStreamSynchronize(d0.s));  // the gather buffer is reused by the next delivery
+        return 0;
     }
     return for_each_gpu(G, [&](int g) -> int {
         if (!src[g]) return 0;
