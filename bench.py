@@ -1,32 +1,43 @@
 #!/usr/bin/env python
 """bench.py — the driver's measurement contract for the FL/RL codec hot path.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload fl|rl4|rl64|rl4096]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload all|fl|rl4|rl64|rl4096|stack16g|stream64g]
 
-One "step" = one pass of the hot path over one batch of synthetic input resident in HBM:
-compress the whole workload, then decompress the result (BASELINE.json configs[1]: FL over
-1 GiB of bytes whose per-frame width is uniform in 1..8; configs[2] for the rl* workloads).
-`value` = uncompressed bytes through the codec per second = 2 * N * n_gpus / step time
-(a step compresses N bytes and decompresses N bytes on every GPU), GB/s, device timed with
-CUDA events, max over ranks.  `e2e` = the same round trip through the host layer of the C
-ABI (flrl_*_gpu_compress / _decompress: HOST buffers in, HOST buffers out, copies inside
-the timed region).  `roofline` is for the slower of the two kernels of the step.
+One "step" = one pass of the hot path over one batch of synthetic input resident in HBM: compress the whole
+workload, then decompress the result.  The headline (`value`, `ms_per_step`, `config.workload`) is BASELINE.json
+configs[1]: FL over 1 GiB of bytes whose per-frame width is uniform in 1..8.  With the default `--workload all` the
+three configs[2] workloads (RL, 1 GiB, geometric runs of mean 4 / 64 / 4096) are measured in the same run and reported
+under `detail.workloads`; `roofline` is the kernel furthest below the HBM roofline over all four.
+`value` = uncompressed bytes through the codec per second = 2 * N * n_gpus / step time (a step compresses N bytes and
+decompresses N bytes on every GPU), GB/s, device timed with CUDA events, max over ranks.  `e2e` = the same round trip
+through the host layer of the C ABI (flrl_*_gpu_compress / _decompress: HOST buffers in, HOST buffers out, copies
+inside the timed region); at N > 1 rank 0 makes ONE call with ngpus = N on the N shards (the product's own multi-GPU
+path: shards, NCCL all-gather of the sizes, every GPU delivers at its offset of the merged container in host memory).
 
-N > 1 (torchrun, one rank per GPU): every rank owns one shard of the same shape (weak
-scaling); the only exchange on the path is the all-gather of the per-shard compressed sizes
-(NCCL, one u64 per GPU) from which every rank computes its output offset on the device.  The
-device-resident concatenation to rank 0 (NCCL send/recv over NVLink) is timed separately
-(detail.concat_to_rank0_ms): end to end each GPU delivers its payload to the host at its offset.
+N > 1 (torchrun, one rank per GPU), default workloads: every rank owns one shard of the same shape (weak scaling).
+Inside the step the ranks all-gather the per-shard compressed sizes (NCCL, one u64 per GPU) and scan them into output
+offsets on the device: the merged container = the shards where they are + this offset table, which is how the product
+delivers (each GPU writes at its offset of the host buffer / file over its own PCIe link).  Gathering the payloads
+into ONE GPU's memory (the reference's gpuNCCLCompress ends like that, fl_gpu.cu:221-238) is bound by that GPU's
+NVLink ingress; it is timed as a second step variant and reported as `detail.concat_in_step_ms` /
+`detail.value_with_concat_to_rank0`, not hidden.
 
-`--impl reference` times the reference's own CPU implementation (oracle/_ref, built from the
-unmodified sources by oracle/Makefile; the oracle port for RL, which the reference lacks) on
-all host cores over a bounded sample.  This file is one of the few allowed users of oracle/.
+`--workload stack16g | stream64g` (BASELINE.json configs[3] / configs[4]): STRONG scaling — the total size is fixed
+(16 / 64 GiB, `--total-bytes` overrides), cut across the ranks with the reference's shard rule (file_io.cu:46-51), FL
+and RL both, same step.  Device generators follow SURVEY.md §8(d) inputs 4 and 5 (tests/test_workloads_gpu.py holds the
+numpy statement used for parity at small sizes).
+
+`--impl reference` times the reference's own CPU implementation (oracle/_ref, built from the unmodified sources by
+oracle/Makefile; the oracle port for RL, which the reference lacks) on all host cores over a bounded sample.  This
+file is one of the few allowed users of oracle/.
 """
 from __future__ import annotations
 
 import argparse
 import importlib
 import json
+import math
 import os
 import subprocess
 import sys
@@ -43,6 +54,13 @@ WORKLOADS = {
     "rl64": "configs[2]: RL 1 GiB synthetic bytes, geometric run lengths mean 64",
     "rl4096": "configs[2]: RL 1 GiB synthetic bytes, geometric run lengths mean 4096",
 }
+BIG = {
+    "stack16g": ("configs[3]: FL+RL on a 16 GiB synthetic BMP-like image stack (24-bit pixels, gradients + noise)", 16 * GIB),
+    "stream64g": ("configs[4]: FL+RL on a 64 GiB sharded synthetic mixed-entropy stream", 64 * GIB),
+}
+# committed `ncu --set full` captures that hold dram__bytes_read.sum + dram__bytes_write.sum per launch (1 GiB workloads)
+NCU_FILES = {"fl": "profiles/r01_run8_fl_ncu_full.csv", "rl4": "profiles/r02_rl4_ncu_full.csv", "rl64": "profiles/r02_rl64_ncu_full.csv",
+             "rl4096": "profiles/r02_rl4096_ncu_full.csv"}
 
 
 def peaks():
@@ -142,78 +160,187 @@ def gen_rl_device(torch, n, mean, seed=None):
     return out
 
 
+def gen_narrow_device(torch, n, g, wmax=4):
+    """Narrow noise: per-frame width w ~ U{1..wmax}, bytes U[0,256) & ((1 << w) - 1)."""
+    frames = (n + 127) // 128
+    w = torch.randint(1, wmax + 1, (frames,), device="cuda", generator=g, dtype=torch.int32)
+    out = torch.empty(frames * 128, dtype=torch.uint8, device="cuda")
+    step = 1 << 21
+    for f0 in range(0, frames, step):
+        f1 = min(frames, f0 + step)
+        d = torch.randint(0, 256, (f1 - f0, 128), device="cuda", generator=g, dtype=torch.int32)
+        d &= ((1 << w[f0:f1]) - 1)[:, None]
+        out[f0 * 128:f1 * 128] = d.to(torch.uint8).reshape(-1)
+    return out[:n]
+
+
+def gen_stream_device(torch, b0, n, seg=1 << 20):
+    """Bytes [b0, b0 + n) of SURVEY.md §8d input 5 on the device: 1 MiB segments cycling zeros / constant runs (mean
+    4096) / narrow noise (w in 1..4) / geometric runs (mean 64) / full-entropy bytes.  All segments of one kind inside
+    the range are drawn in one batch (seeded by kind and first segment), so this is the device analogue of the numpy
+    statement in tests/test_workloads_gpu.py, not the same bytes."""
+    assert b0 % seg == 0
+    s0, nseg = b0 // seg, (n + seg - 1) // seg
+    out = torch.empty(nseg * seg, dtype=torch.uint8, device="cuda")
+    view = out.view(nseg, seg)
+    for kind in range(5):
+        first = (kind - s0) % 5
+        c = len(range(first, nseg, 5))
+        if c == 0:
+            continue
+        g = torch.Generator(device="cuda").manual_seed(1000 * (s0 + first) + kind)
+        if kind == 0:
+            batch = torch.zeros(c * seg, dtype=torch.uint8, device="cuda")
+        elif kind == 1:
+            batch = gen_rl_device(torch, c * seg, 4096, seed=7 + s0 + first)
+        elif kind == 2:
+            batch = gen_narrow_device(torch, c * seg, g)
+        elif kind == 3:
+            batch = gen_rl_device(torch, c * seg, 64, seed=11 + s0 + first)
+        else:
+            batch = torch.randint(0, 256, (c * seg,), device="cuda", generator=g, dtype=torch.uint8)
+        view[first::5] = batch.view(c, seg)
+        del batch
+    return out[:n]
+
+
+IMG_W, IMG_H, IMG_HDR = 1280, 853, 138
+IMG_PIX = 3275520
+IMG_BYTES = IMG_HDR + IMG_PIX  # 3,275,658: the size of example_input/sample_1280x853.bmp
+
+
+def gen_stack_device(torch, b0, n, batch=32):
+    """Bytes [b0, b0 + n) of SURVEY.md §8d input 4 on the device: a stack of 1280x853 24-bit images behind 138-byte
+    headers; channel value clamp(A_c x/W + B_c y/H + 8 sin(2 pi (x+y)/64) + noise), noise ~ U{-k..k}, k cycling {0, 1, 3}
+    per image (flat bands for RL, dark regions for FL)."""
+    i0, i1 = b0 // IMG_BYTES, (b0 + n + IMG_BYTES - 1) // IMG_BYTES
+    x = torch.arange(IMG_W, dtype=torch.float32, device="cuda")[None, :, None]
+    y = torch.arange(IMG_H, dtype=torch.float32, device="cuda")[:, None, None]
+    A = torch.tensor([200.0, 90.0, 30.0], device="cuda")[None, None, :]
+    B = torch.tensor([20.0, 120.0, 210.0], device="cuda")[None, None, :]
+    base = (A * x / IMG_W + B * y / IMG_H + 8 * torch.sin(2 * math.pi * (x + y) / 64)).reshape(-1)[:IMG_PIX]
+    hdr = torch.zeros(IMG_HDR, dtype=torch.uint8, device="cuda")
+    hdr[0], hdr[1], hdr[10] = 0x42, 0x4D, IMG_HDR
+    out = torch.empty((i1 - i0) * IMG_BYTES, dtype=torch.uint8, device="cuda")
+    rows = out.view(i1 - i0, IMG_BYTES)
+    rows[:, :IMG_HDR] = hdr
+    g = torch.Generator(device="cuda").manual_seed(i0)
+    for j0 in range(i0, i1, batch):
+        j1 = min(i1, j0 + batch)
+        k = torch.tensor([(0, 1, 3)[j % 3] for j in range(j0, j1)], device="cuda", dtype=torch.int16)[:, None]
+        r = torch.randint(0, 7, (j1 - j0, IMG_PIX), device="cuda", generator=g, dtype=torch.int16)
+        noise = torch.where(k == 3, r - 3, torch.where(k == 1, r % 3 - 1, torch.zeros_like(r)))
+        rows[j0 - i0:j1 - i0, IMG_HDR:] = (base[None, :] + noise).clamp_(0, 255).to(torch.uint8)
+        del r, noise
+    lo = b0 - i0 * IMG_BYTES
+    return out[lo:lo + n]
+
+
+def run_before_device(torch, d, a):
+    """Number of bytes equal to d[a] immediately before position a (the prev_run of a shard cut at a)."""
+    if a == 0:
+        return 0
+    v, look = d[a], 1 << 16
+    while True:
+        lo = max(0, a - look)
+        same = (d[lo:a] == v).flip(0)
+        r = int(same.to(torch.int8).cummin(0).values.sum(dtype=torch.int64).item())
+        if r < a - lo or lo == 0:
+            return r
+        look *= 16
+
+
 # ------------------------------------------------------------------------------ our arm
-class FLWork:
-    """Device-resident FL round trip on the current device (through the C ABI's device layer)."""
+class Work:
+    """Device-resident round trip of one shard on the current device through the C ABI's device layer.  The shard is
+    encoded and decoded in pieces of at most `piece` bytes (one piece for the 1 GiB workloads): FL pieces are cut at
+    multiples of 128 bytes, RL pieces carry prev_run and 255 bytes of look-ahead, so piece outputs concatenate to the
+    single-stream output (include/flrl.h shard semantics)."""
 
-    kernels = ("fl_encode_kernel", "fl_decode_kernel")
+    def __init__(self, flrl, torch, kind, d_in, piece=None):
+        self.flrl, self.torch, self.kind, self.d_in = flrl, torch, kind, d_in
+        n = self.n = d_in.numel()
+        piece = n if not piece else min(n, piece - piece % 128)
+        self.cuts = [(a, min(n, a + piece)) for a in range(0, n, piece)]
+        pmax = max(b - a for a, b in self.cuts)
+        self.kernels = ("fl_encode_kernel", "fl_decode_kernel") if kind == "fl" else ("rl_encode_kernel", "rl_decode_kernel")
+        self.enc = flrl.FLEncoder(pmax) if kind == "fl" else flrl.RLEncoder(pmax)
+        self.dec = flrl.FLDecoder(pmax) if kind == "fl" else flrl.RLDecoder(pmax)
+        self.prev = [0 if kind == "fl" else run_before_device(torch, d_in, a) for a, _ in self.cuts]
+        self.total_size = torch.zeros(1, dtype=torch.int64, device="cuda")
+        # first pass: per-piece compressed sizes (the decoder's launch arguments) and the round-trip check
+        self.sizes, self.csize, self.alg_bytes = [], 0, 0
+        for i, (a, b) in enumerate(self.cuts):
+            self._encode(i)
+            if kind == "fl":
+                bits, values = self.enc.result(b - a)
+                self.sizes.append((bits.numel(), values.numel()))
+                self.csize += bits.numel() + values.numel()
+                self.alg_bytes += (b - a) + bits.numel() + values.numel()  # SURVEY.md §8d: N + F + valuesSize, both directions
+            else:
+                counts, _ = self.enc.result()
+                self.sizes.append((counts.numel(),))
+                self.csize += 2 * counts.numel()
+                self.alg_bytes += (b - a) + 2 * counts.numel()  # SURVEY.md §8d: N + 2P
+            self._decode(i)
+            out = self.dec.result(b - a) if kind == "fl" else self.dec.result()
+            assert torch.equal(out, d_in[a:b]), f"{kind} round trip failed (piece {i})"
 
-    def __init__(self, flrl, torch, n, rank):
-        self.flrl, self.torch, self.n = flrl, torch, n
-        self.d_in, w = gen_fl_device(torch, n, seed=42 + rank)
-        self.enc, self.dec = flrl.FLEncoder(n), flrl.FLDecoder(n)
-        self.enc.launch(self.d_in)
-        self.bits, self.values = self.enc.result(n)
-        assert torch.equal(self.bits.to(torch.int32), w), "FL widths differ from the generator's"
-        self.csize = self.values.numel()
-        self.alg_bytes = n + self.bits.numel() + self.csize  # SURVEY.md §8d: N + F + valuesSize, both directions
-        self.dec.launch(self.bits, self.values, n)
-        assert torch.equal(self.dec.result(n), self.d_in), "FL round trip failed"
+    def _encode(self, i):
+        a, b = self.cuts[i]
+        if self.kind == "fl":
+            self.enc.launch(self.d_in[a:b])
+        else:
+            self.enc.launch(self.d_in[a:min(self.n, b + 255)], n=b - a, prev_run=self.prev[i])
 
-    def encode(self):
-        self.enc.launch(self.d_in)
+    def _decode(self, i):
+        a, b = self.cuts[i]
+        if self.kind == "fl":
+            nb, nv = self.sizes[i]
+            self.dec.launch(self.enc.bits[:nb], self.enc.values[:nv], b - a)
+        else:
+            (p,) = self.sizes[i]
+            self.dec.launch(self.enc.counts[:p], self.enc.values[:p])
 
-    def decode(self):
-        self.dec.launch(self.bits, self.values, self.n)
-
-    def size_tensor(self):
-        return self.enc.size
+    def step(self, exchange=None, events=None):
+        """compress the shard, [exchange the sizes], decompress it; pieces back to back."""
+        self.total_size.zero_()
+        for i in range(len(self.cuts)):
+            if events:
+                events[i][0].record()
+            self._encode(i)
+            if events:
+                events[i][1].record()
+            self.total_size += self.enc.size
+            if exchange and i == len(self.cuts) - 1:
+                exchange()
+            if events:
+                events[i][2].record()
+            self._decode(i)
+            if events:
+                events[i][3].record()
 
     def payload(self):
-        return self.enc.values
+        return self.enc.values if self.kind == "fl" else self.enc.counts
 
 
-class RLWork:
-    kernels = ("rl_encode_kernel", "rl_decode_kernel")
-
-    def __init__(self, flrl, torch, n, rank, mean):
-        self.flrl, self.torch, self.n = flrl, torch, n
-        self.d_in = gen_rl_device(torch, n, mean, seed=mean + 7919 * rank)
-        self.enc, self.dec = flrl.RLEncoder(n), flrl.RLDecoder(n)
-        self.enc.launch(self.d_in)
-        self.counts, self.vals = self.enc.result()
-        self.pairs = self.counts.numel()
-        self.csize = 2 * self.pairs
-        self.alg_bytes = n + 2 * self.pairs  # SURVEY.md §8d: N + 2P
-        self.dec.launch(self.counts, self.vals)
-        assert torch.equal(self.dec.result(), self.d_in), "RL round trip failed"
-
-    def encode(self):
-        self.enc.launch(self.d_in)
-
-    def decode(self):
-        self.dec.launch(self.counts, self.vals)
-
-    def size_tensor(self):
-        return self.enc.size
-
-    def payload(self):
-        return self.enc.counts
-
-
-def make_work(flrl, torch, workload, n, rank):
+def make_input(torch, workload, n, rank, world, total):
+    """The rank's shard of the workload on the device + (begin, length) of the shard in the whole workload."""
+    sharding = importlib.import_module("fl-rl-compression-mpi_b200.sharding")
     if workload == "fl":
-        return FLWork(flrl, torch, n, rank)
-    return RLWork(flrl, torch, n, rank, int(workload[2:]))
+        return gen_fl_device(torch, n, seed=42 + rank)[0], (rank * n, n)
+    if workload.startswith("rl"):
+        mean = int(workload[2:])
+        return gen_rl_device(torch, n, mean, seed=mean + 7919 * rank), (rank * n, n)
+    b0, m = sharding.shard_range(total, world, rank)  # the reference's rule, file_io.cu:46-51
+    gen = gen_stack_device if workload == "stack16g" else gen_stream_device
+    return gen(torch, b0, m), (b0, m)
 
 
-def e2e_round_trip(flrl, torch, workload, work, steps, warmup):
-    """The same metric through the host layer of the C ABI: pinned HOST buffers in, HOST buffers out,
-    H2D / D2H inside the timed region.  Returns (seconds per step, h2d bytes, d2h bytes) or None."""
-    if not hasattr(flrl, "HostCodec"):
-        return None
-    hc = flrl.HostCodec(workload[:2], work.n)
-    hc.load_input(work.d_in)  # device -> pinned host, untimed: this is the "file in host memory"
+def e2e_round_trip(flrl, torch, kind, host_in, ngpus, steps, warmup):
+    """The same metric through the host layer of the C ABI: pinned HOST buffers in, HOST buffers out, H2D / D2H inside
+    the timed region.  host_in: a HostCodec whose input is loaded.  Returns (seconds per step, h2d bytes, d2h bytes, per-GPU figures)."""
+    hc = host_in
     for _ in range(max(1, min(warmup, 2))):
         hc.compress()
         hc.decompress()
@@ -226,7 +353,147 @@ def e2e_round_trip(flrl, torch, workload, work, steps, warmup):
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / steps
     comp = hc.compressed_bytes()
-    return dt, work.n + comp, comp + work.n
+    return dt, hc.n + comp, comp + hc.n, hc.timing_per_gpu()
+
+
+def measure(args, torch, dist, flrl, sharding, workload, kind, rank, local, world, headline):
+    """Times `args.steps` steps of one workload / codec on every rank; returns rank-0's dict (None elsewhere)."""
+    big = workload in BIG
+    total = args.total_bytes or (BIG[workload][1] if big else args.bytes * world)
+    d_in, (b0, n) = make_input(torch, workload, args.bytes, rank, world, total)
+    work = Work(flrl, torch, kind, d_in, piece=args.piece_bytes if big else None)
+    sizes = torch.zeros(world, dtype=torch.int64, device="cuda")
+    offsets = torch.zeros(world, dtype=torch.int64, device="cuda")
+
+    def exchange():
+        """N > 1, inside every timed step: the ONLY exchange of the path — all-gather the per-shard compressed sizes
+        (one u64 per GPU, NCCL) and turn them into output offsets by an exclusive scan, on the device, no host sync."""
+        sharding.exchange_sizes(dist, work.total_size, sizes, offsets)  # the logic tests/test_sharding_gloo.py runs over gloo
+
+    ex = exchange if world > 1 else None
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    for _ in range(args.warmup):
+        work.step(ex)
+    torch.cuda.synchronize()
+    ke = [[(ev(), ev(), ev(), ev()) for _ in work.cuts] for _ in range(args.steps)]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0 and headline:
+        # nvidia-smi delivers one sample per 100 ms and the timed region is a few ms: keep the same load running
+        # (untimed, no collective) until the sampler has produced samples, then enter the timed region without a gap.
+        sampler.start()
+        t_wait = time.perf_counter()
+        while len(sampler.lines) < 4 and time.perf_counter() - t_wait < 3.0:
+            work.step(None)
+            torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t_begin, t_end = ev(), ev()
+    t_begin.record()
+    for e in ke:
+        work.step(ex, e)
+    t_end.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clocks = sampler.stop() if rank == 0 and headline else None
+    total_ms = t_begin.elapsed_time(t_end)
+    enc_ms = sum(a.elapsed_time(b) for e in ke for a, b, _, _ in e) / args.steps
+    dec_ms = sum(c.elapsed_time(d) for e in ke for _, _, c, d in e) / args.steps
+    stats = torch.tensor([total_ms, enc_ms, dec_ms, float(work.alg_bytes), float(work.csize)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+        total_ms, enc_ms, dec_ms = mx[:3].tolist()
+        alg_all, csize_all = stats[3].item(), stats[4].item()
+    else:
+        alg_all, csize_all = float(work.alg_bytes), float(work.csize)
+    ms_per_step = total_ms / args.steps
+
+    # the same step with the payloads gathered into rank 0's memory (the reference's merged-on-rank-0 result)
+    concat_ms = concat_step_ms = None
+    if world > 1 and len(work.cuts) == 1 and not args.no_concat:
+        gather_buf = torch.empty(int(sum(sizes.tolist())) + 16, dtype=torch.uint8, device="cuda") if rank == 0 else None
+        pay = 1 if kind == "fl" else 2  # FL: values (the widths' places are known a priori); RL: counts and values
+
+        def concat():
+            for _ in range(pay):
+                sharding.concat_to_rank0(dist, work.payload(), sizes, rank, gather_buf)
+
+        work.step(ex)
+        concat()  # warm-up (NCCL p2p channels)
+        torch.cuda.synchronize()
+        dist.barrier()
+        c0, c1, c2 = ev(), ev(), ev()
+        c0.record()
+        for _ in range(3):
+            concat()
+        c1.record()
+        for _ in range(3):
+            work.step(ex)
+            concat()
+        c2.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([c0.elapsed_time(c1) / 3, c1.elapsed_time(c2) / 3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        concat_ms, concat_step_ms = round(t[0].item(), 4), round(t[1].item(), 4)
+        del gather_buf
+
+    # end to end through the host layer
+    e2e = None
+    if not args.no_e2e and (headline or world == 1):
+        e2e_n = n if not big else min(n, args.e2e_bytes // world)
+        steps = max(1, min(args.steps, 3 if big else 5))
+        hc = flrl.HostCodec(kind, e2e_n, ngpus=1)
+        hc.load_input(d_in[:e2e_n])
+        dt, h2d, d2h, _ = e2e_round_trip(flrl, torch, kind, hc, 1, steps, args.warmup)
+        del hc
+        per_rank = None
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            per_rank = round(2 * e2e_n * world / t.item() / 1e9, 3)
+            # ONE call of the product's multi-GPU API from rank 0 over all shards while the other ranks wait on the host
+            # (gloo barrier: their GPUs stay idle).  The shards travel to rank 0's pinned input buffer first, untimed:
+            # this is "the file in host memory".
+            gathered = [torch.empty(e2e_n, dtype=torch.uint8, device="cuda") for _ in range(world)] if rank == 0 else None
+            dist.gather(d_in[:e2e_n].contiguous(), gathered, dst=0)
+            torch.cuda.synchronize()
+            if rank == 0:
+                hcN = flrl.HostCodec(kind, e2e_n * world, ngpus=world)
+                for r in range(world):
+                    hcN.src.array[r * e2e_n:(r + 1) * e2e_n] = gathered[r].cpu().numpy()
+                del gathered
+                dt, h2d, d2h, per_gpu = e2e_round_trip(flrl, torch, kind, hcN, world, steps, args.warmup)
+                del hcN
+            dist.barrier(group=args.host_group)
+        if rank == 0:
+            api = "flrl_%s_gpu_compress_into + flrl_%s_gpu_decompress_into (include/flrl.h), pinned host buffers, ngpus=%d" % (kind, kind, world)
+            e2e = {"value": round(2 * e2e_n * world / dt / 1e9, 3), "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                   "api": api, "bytes": e2e_n * world}
+            if per_rank is not None:
+                e2e["per_rank_calls_value"] = per_rank  # N processes, each calling the 1-GPU host API on its shard
+            if big and e2e_n < n:
+                e2e["note"] = f"first {e2e_n} bytes of every shard (pinned host memory bounds the e2e sample)"
+    if rank != 0:
+        return None
+    peak, _ = peaks()
+    nbytes_all = total if big else args.bytes * world
+    return {
+        "workload": workload, "codec": kind, "bytes": int(nbytes_all), "compressed_bytes": int(csize_all),
+        "value": round(2 * nbytes_all / (ms_per_step * 1e-3) / 1e9, 3), "ms_per_step": round(ms_per_step, 4),
+        "compress_ms": round(enc_ms, 4), "decompress_ms": round(dec_ms, 4),
+        "compress_gbs": round(nbytes_all / world / enc_ms / 1e6, 2), "decompress_gbs": round(nbytes_all / world / dec_ms / 1e6, 2),
+        "compress_frac_of_hbm": round(alg_all / world / enc_ms / 1e6 / peak, 4),
+        "decompress_frac_of_hbm": round(alg_all / world / dec_ms / 1e6 / peak, 4),
+        "algorithmic_bytes_per_gpu": int(alg_all / world), "pieces_per_gpu": len(work.cuts), "kernels": work.kernels,
+        "concat_to_rank0_ms": concat_ms, "concat_in_step_ms": concat_step_ms,
+        "value_with_concat_to_rank0": round(2 * nbytes_all / (concat_step_ms * 1e-3) / 1e9, 3) if concat_step_ms else None,
+        "e2e": e2e, "clocks": clocks, "gpu_launches": 2 * args.steps * len(work.cuts),
+    }
 
 
 def run_ours(args):
@@ -239,160 +506,71 @@ def run_ours(args):
     if world != args.gpus and world > 1:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
+    args.host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        args.host_group = dist.new_group(backend="gloo")  # host-side barrier: waiting ranks leave their GPUs idle
     flrl = importlib.import_module("fl-rl-compression-mpi_b200")  # raises if libflrl.so is missing: no fallback
     sharding = importlib.import_module("fl-rl-compression-mpi_b200.sharding")
-    n = args.bytes
-    work = make_work(flrl, torch, args.workload, n, rank)
-
-    sizes = torch.zeros(world, dtype=torch.int64, device="cuda")
-    gather_buf = None
-    if world > 1 and rank == 0:
-        gather_buf = torch.empty(world * ((n + 15) // 16 * 16), dtype=torch.uint8, device="cuda")
-
-    offsets = torch.zeros(world, dtype=torch.int64, device="cuda")
-
-    def exchange():
-        """N > 1, inside every timed step: the ONLY exchange of the path — all-gather the per-shard compressed sizes
-        (one u64 per GPU, NCCL) and turn them into output offsets by an exclusive scan, on the device, no host sync."""
-        sharding.exchange_sizes(dist, work.size_tensor(), sizes, offsets)  # the logic tests/test_sharding_gloo.py runs over gloo
-
-    def concat_to_rank0():
-        """The device-resident merge of the reference's gpuNCCLCompress (fl_gpu.cu:221-238): every rank sends its payload
-        to its offset in rank 0's buffer (NCCL send/recv over NVLink).  It serialises on rank 0's ingress link, so it
-        is measured on its own (detail.concat_to_rank0_ms) and is not part of the timed step: end to end, every GPU
-        delivers its payload straight to its offset in the host buffer instead (host layer, e2e)."""
-        sharding.concat_to_rank0(dist, work.payload(), sizes, rank, gather_buf)
-
-    def step():
-        work.encode()
-        if world > 1:
-            exchange()
-        work.decode()
-
-    def step_local():  # no collective: rank 0 alone runs it while waiting for clock samples
-        work.encode()
-        work.decode()
-
-    ev = lambda: torch.cuda.Event(enable_timing=True)
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
-    # per-kernel launch durations, measured live on the launching stream (torch's current stream)
-    ke = [(ev(), ev(), ev(), ev()) for _ in range(args.steps)]
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        # nvidia-smi delivers one sample per 100 ms and the timed region is a few ms: keep the same load running
-        # (untimed) until the sampler has produced samples, then enter the timed region without a gap.
-        sampler.start()
-        t_wait = time.perf_counter()
-        while len(sampler.lines) < 4 and time.perf_counter() - t_wait < 3.0:
-            step_local()
-            torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t_begin, t_end = ev(), ev()
-    t_begin.record()
-    for a, b, c, d in ke:
-        a.record()
-        work.encode()
-        b.record()
-        if world > 1:
-            exchange()
-        c.record()
-        work.decode()
-        d.record()
-    t_end.record()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    clocks = sampler.stop() if rank == 0 else None
-    total_ms = t_begin.elapsed_time(t_end)
-    enc_ms = sum(a.elapsed_time(b) for a, b, _, _ in ke) / args.steps
-    dec_ms = sum(c.elapsed_time(d) for _, _, c, d in ke) / args.steps
-    if world > 1:
-        t = torch.tensor([total_ms, enc_ms, dec_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, enc_ms, dec_ms = t.tolist()
-    ms_per_step = total_ms / args.steps
-    concat_ms = None
-    if world > 1:
-        exchange()
-        concat_to_rank0()  # warm-up (NCCL p2p channels)
-        torch.cuda.synchronize()
-        dist.barrier()
-        c0, c1 = ev(), ev()
-        c0.record()
-        for _ in range(3):
-            concat_to_rank0()
-        c1.record()
-        torch.cuda.synchronize()
-        t = torch.tensor([c0.elapsed_time(c1) / 3], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        concat_ms = round(t.item(), 4)
-
-    e2e = None
-    if not args.no_e2e:
-        r = e2e_round_trip(flrl, torch, args.workload, work, max(1, min(args.steps, 5)), args.warmup)
-        if r is not None:
-            dt, h2d, d2h = r
-            if world > 1:
-                t = torch.tensor([dt], dtype=torch.float64, device="cuda")
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                dt = t.item()
-            e2e = {"value": round(2 * n * world / dt / 1e9, 3), "unit": "GB/s", "h2d_bytes_per_step": h2d,
-                   "d2h_bytes_per_step": d2h, "api": "flrl_%s_gpu_compress + flrl_%s_gpu_decompress (include/flrl.h), pinned host buffers"
-                   % (args.workload[:2], args.workload[:2])}
-
+    big = args.workload in BIG
+    if big:
+        plan = [(args.workload, "fl"), (args.workload, "rl")]
+    elif args.workload == "all":
+        plan = [("fl", "fl"), ("rl4", "rl"), ("rl64", "rl"), ("rl4096", "rl")]
+    else:
+        plan = [(args.workload, args.workload[:2])]
+    results = []
+    for i, (w, kind) in enumerate(plan):
+        r = measure(args, torch, dist, flrl, sharding, w, kind, rank, local, world, headline=(i == 0))
+        results.append(r)
+        torch.cuda.empty_cache()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     peak, peak_src = peaks()
-    slow = 0 if enc_ms >= dec_ms else 1
-    k_ms = (enc_ms, dec_ms)[slow]
-    achieved = work.alg_bytes / (k_ms * 1e-3) / 1e9
+    head = results[0]
+    # the kernel furthest below the HBM roofline over everything measured in this run
+    worst = None
+    for r in results:
+        for k, frac, ms in ((r["kernels"][0], r["compress_frac_of_hbm"], r["compress_ms"]), (r["kernels"][1], r["decompress_frac_of_hbm"], r["decompress_ms"])):
+            if worst is None or frac < worst[2]:
+                worst = (r, k, frac, ms)
+    wr, wk, wfrac, wms = worst
+    achieved = wr["algorithmic_bytes_per_gpu"] / (wms * 1e-3) / 1e9
+    label = BIG[args.workload][0] if big else WORKLOADS[head["workload"]]
+    par = "1 GPU"
+    if world > 1:
+        par = ("contiguous shards of ONE workload (reference rule, file_io.cu:46-51), " if big else "one shard of the same shape per GPU, ") + \
+              "NCCL all-gather of the shard sizes + device-side offset scan in every step; merged container = shards in place + offsets " \
+              "(gathering into one GPU: detail.concat_in_step_ms)"
     line = {
         "metric": "FL/RL compress & decompress GB/s (uncompressed)",
-        "value": round(2 * n * world / (ms_per_step * 1e-3) / 1e9, 3),
-        "unit": "GB/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "value": head["value"], "unit": "GB/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": head["ms_per_step"],
+        "higher_is_better": True, "scaling": "strong" if big else "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload], "bytes_per_gpu": n, "compressed_bytes_per_gpu": int(work.csize),
-                   "step": "compress N bytes then decompress them, per GPU",
-                   "l2": "inputs larger than L2 (1 GiB per pass vs 126 MB)",
-                   "parallelism": "contiguous shards, one per GPU; NCCL all-gather of the shard sizes + device-side offset scan in every step" if world > 1 else "1 GPU"},
-        "detail": {"compress_gbs": round(n / enc_ms / 1e6, 2), "decompress_gbs": round(n / dec_ms / 1e6, 2),
-                   "compress_ms": round(enc_ms, 4), "decompress_ms": round(dec_ms, 4), "concat_to_rank0_ms": concat_ms,
-                   "compress_frac_of_hbm": round(work.alg_bytes / enc_ms / 1e6 / peak, 4),
-                   "decompress_frac_of_hbm": round(work.alg_bytes / dec_ms / 1e6 / peak, 4)},
-        "roofline": {"bound": "hbm", "kernel": work.kernels[slow], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": TRAFFIC.get((args.workload, work.kernels[slow])) if n == GIB else None,
-                     "algorithmic_bytes": int(work.alg_bytes), "launch_ms": round(k_ms, 4), "peak_source": peak_src},
-        "e2e": e2e,
-        "gpu_launches": 2 * args.steps,
-        "clocks": clocks,
+        "config": {"workload": label, "codec": head["codec"], "bytes_total": head["bytes"], "compressed_bytes_total": head["compressed_bytes"],
+                   "step": "compress the workload then decompress it (device-resident)",
+                   "l2": "inputs larger than L2 (>= 1 GiB per pass vs 126 MB)", "parallelism": par,
+                   "concat_inside_step": False},
+        "detail": {"compress_gbs": head["compress_gbs"], "decompress_gbs": head["decompress_gbs"], "compress_ms": head["compress_ms"],
+                   "decompress_ms": head["decompress_ms"], "compress_frac_of_hbm": head["compress_frac_of_hbm"],
+                   "decompress_frac_of_hbm": head["decompress_frac_of_hbm"], "concat_to_rank0_ms": head["concat_to_rank0_ms"],
+                   "concat_in_step_ms": head["concat_in_step_ms"], "value_with_concat_to_rank0": head["value_with_concat_to_rank0"],
+                   "workloads": {(r["workload"] if not big else r["workload"] + "/" + r["codec"]): {k: v for k, v in r.items() if k not in ("clocks",)} for r in results}},
+        "roofline": {"bound": "hbm", "kernel": wk, "workload": wr["workload"], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(achieved / peak, 4), "traffic": None, "traffic_source": NCU_FILES.get(wr["workload"]),
+                     "algorithmic_bytes": wr["algorithmic_bytes_per_gpu"], "launch_ms": wms, "peak_source": peak_src},
+        "e2e": head["e2e"],
+        "gpu_launches": head["gpu_launches"],
+        "clocks": head["clocks"],
     }
-    if not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(args.workload, threads=1, budget_s=12.0)
+    if not args.no_cpu_baseline and world == 1 and not big:
+        line["cpu_baseline"] = cpu_baseline("fl" if head["workload"] == "fl" else head["workload"], threads=1, budget_s=12.0)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
-
-
-# dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) from the committed `ncu --set full` captures
-# (profiles/r01_run8_fl_ncu_full.csv for FL, r01_run7_*_ncu_full.csv for RL; 1 GiB per launch, the bench's default size)
-TRAFFIC = {
-    ("fl", "fl_encode_kernel"): 1_643_363_000, ("fl", "fl_decode_kernel"): 1_640_467_000,
-    ("rl4", "rl_encode_kernel"): 1_578_695_000, ("rl4", "rl_decode_kernel"): 1_558_388_000,
-    ("rl64", "rl_encode_kernel"): 1_110_706_000, ("rl64", "rl_decode_kernel"): 1_054_236_000,
-    ("rl4096", "rl_encode_kernel"): 1_087_804_000, ("rl4096", "rl_decode_kernel"): 1_028_774_000,
-}
 
 
 # ------------------------------------------------------- CPU baseline / reference arm
@@ -529,15 +707,21 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
-    ap.add_argument("--workload", choices=list(WORKLOADS), default="fl")
-    ap.add_argument("--bytes", type=int, default=GIB, help="uncompressed bytes per GPU (default: the 1 GiB of the config)")
+    ap.add_argument("--workload", choices=["all"] + list(WORKLOADS) + list(BIG), default="all")
+    ap.add_argument("--bytes", type=int, default=GIB, help="uncompressed bytes per GPU of the 1 GiB workloads")
+    ap.add_argument("--total-bytes", type=int, default=0, help="stack16g / stream64g: total size over all GPUs (default 16 / 64 GiB)")
+    ap.add_argument("--piece-bytes", type=int, default=4 * GIB, help="stack16g / stream64g: bytes per kernel launch")
+    ap.add_argument("--e2e-bytes", type=int, default=4 * GIB, help="stack16g / stream64g: bytes of the end-to-end sample (pinned host memory)")
     ap.add_argument("--ref-chunk-bytes", type=int, default=16 << 20)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-concat", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "ours" and args.warmup < 3:
         args.warmup = 3  # timing rule: W >= 3
     if args.impl == "reference":
+        if args.workload in BIG or args.workload == "all":
+            args.workload = "fl"  # the reference arm times the headline workload
         run_reference(args)
     else:
         run_ours(args)
