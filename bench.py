@@ -334,7 +334,37 @@ def make_input(torch, workload, n, rank, world, total):
         return gen_rl_device(torch, n, mean, seed=mean + 7919 * rank), (rank * n, n)
     b0, m = sharding.shard_range(total, world, rank)  # the reference's rule, file_io.cu:46-51
     gen = gen_stack_device if workload == "stack16g" else gen_stream_device
-    return gen(torch, b0, m), (b0, m)
+    d = gen(torch, b0, m)
+    if d.data_ptr() % 16:  # the device layer wants 16-byte aligned buffers (a shard of the stack starts inside an image)
+        d = d.clone()
+    return d, (b0, m)
+
+
+def pcie_probe(torch, devices):
+    """Pinned host <-> device copy bandwidth of this box, both directions at once on every device of `devices`
+    (GB/s per GPU and direction): the ceiling of any host-buffer round trip (tools/pcie_ceiling.cu is the full table)."""
+    n, reps = 128 << 20, 4
+    st = []
+    for dv in devices:
+        with torch.cuda.device(dv):
+            st.append((torch.empty(n, dtype=torch.uint8).pin_memory(), torch.empty(n, dtype=torch.uint8).pin_memory(),
+                       torch.empty(n, dtype=torch.uint8, device=f"cuda:{dv}"), torch.empty(n, dtype=torch.uint8, device=f"cuda:{dv}"),
+                       torch.cuda.Stream(device=dv), torch.cuda.Stream(device=dv)))
+
+    def go():
+        for hi, ho, di, do, s0, s1 in st:
+            for _ in range(reps):
+                with torch.cuda.stream(s0):
+                    di.copy_(hi, non_blocking=True)
+                with torch.cuda.stream(s1):
+                    ho.copy_(do, non_blocking=True)
+        for dv in devices:
+            torch.cuda.synchronize(dv)
+
+    go()
+    t0 = time.perf_counter()
+    go()
+    return n * reps / (time.perf_counter() - t0) / 1e9
 
 
 def e2e_round_trip(flrl, torch, kind, host_in, ngpus, steps, warmup):
@@ -476,6 +506,11 @@ def measure(args, torch, dist, flrl, sharding, workload, kind, rank, local, worl
                    "api": api, "bytes": e2e_n * world}
             if per_rank is not None:
                 e2e["per_rank_calls_value"] = per_rank  # N processes, each calling the 1-GPU host API on its shard
+            if headline:
+                bw = pcie_probe(torch, list(range(world)))
+                e2e["pcie_duplex_gbs_per_gpu_per_direction"] = round(bw, 1)
+                # a round trip moves max(in, out) = the uncompressed bytes over each GPU's link twice: ceiling = that bandwidth x GPUs
+                e2e["frac_of_pcie"] = round(e2e["value"] / (bw * world), 3)
             if big and e2e_n < n:
                 e2e["note"] = f"first {e2e_n} bytes of every shard (pinned host memory bounds the e2e sample)"
     if rank != 0:
