@@ -637,10 +637,11 @@ int fl_decompress_shard(Dev& d, size_t n, const uint8_t* values, uint64_t tail_b
         });
 }
 
-// RL compress of one shard: data[b0 .. b0 + n) of a stream of `size` bytes.  Pairs go straight to the host when
+// RL compress of one shard: data[b0 .. b0 + n) of `size` available bytes (the bytes to encode + the caller's look-ahead),
+// stream_prev = bytes equal to data[0] immediately before data[0].  Pairs go straight to the host when
 // counts_host is given (shard 0), else they are appended to d.a / d.b and delivered after the size exchange.
-int rl_compress_shard(Dev& d, const uint8_t* data, size_t size, size_t b0, size_t n, uint8_t* counts_host, uint8_t* values_host,
-                      size_t pair_cap, uint64_t* total)
+int rl_compress_shard(Dev& d, const uint8_t* data, size_t size, uint64_t stream_prev, size_t b0, size_t n, uint8_t* counts_host,
+                      uint8_t* values_host, size_t pair_cap, uint64_t* total)
 {
     const size_t CH = pipe_chunk_bytes();
     const size_t nch = (n + CH - 1) / CH;
@@ -652,6 +653,7 @@ int rl_compress_shard(Dev& d, const uint8_t* data, size_t size, size_t b0, size_
     // previous chunk is carried over, so no chunk looks back further than one chunk — except the shard's first)
     std::vector<uint64_t> prev(nch, 0);
     prev[0] = run_before(data, b0, b0);
+    if (prev[0] == b0) prev[0] += stream_prev;  // the run reaches back to the start of the data: it continues the caller's
     for (size_t i = 1; i < nch; ++i) {
         const size_t c0 = b0 + i * CH;
         uint64_t r = run_before(data, c0, CH);
@@ -990,13 +992,14 @@ int flrl_fl_gpu_decompress(size_t output_size, const uint8_t* bits, size_t bits_
 extern "C" {
 
 // ------------------------------------------------------------------------------------ RL compress
-int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8_t* counts, uint8_t* values, size_t pair_cap,
-                              size_t* pairs)
+int flrl_rl_gpu_compress_part_into(const uint8_t* data, size_t size, size_t lookahead, uint64_t prev_run, int ngpus, uint8_t* counts,
+                                   uint8_t* values, size_t pair_cap, size_t* pairs)
 {
     if (!pairs) return fail(FLRL_E_ARG, "flrl_rl_gpu_compress: NULL size output");
     *pairs = 0;
     if (size == 0) return FLRL_OK;
     if (!data || !counts || !values) return fail(FLRL_E_ARG, "flrl_rl_gpu_compress: NULL buffer");
+    const size_t avail = size + lookahead;  // bytes behind `data`: pairs start in [0, size), counts may look into the rest
     std::lock_guard<std::mutex> lk(g_host_mu);
     DeviceGuard restore;
     int G = 1;
@@ -1012,12 +1015,13 @@ int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
         shard_range(size, G, g, 128, &b0, &n);
         if (piped) {
             const bool direct = g == 0 && !(G > 1 && g_concat_peer);  // shard 0's pairs start at pair 0
-            if (int r = rl_compress_shard(d, data, size, b0, n, direct ? counts : nullptr, direct ? values : nullptr, pair_cap, &mine[g])) return r;
+            if (int r = rl_compress_shard(d, data, avail, prev_run, b0, n, direct ? counts : nullptr, direct ? values : nullptr, pair_cap, &mine[g])) return r;
             return post_size(d, mine[g]);
         }
         // bytes equal to the shard's first byte immediately before it: the run the shard continues
-        const uint64_t prev = run_before(data, b0, b0);
-        const size_t ahead = std::min<size_t>(255, size - (b0 + n));  // look-ahead: a pair that starts here gets its full count
+        uint64_t prev = run_before(data, b0, b0);
+        if (prev == b0) prev += prev_run;
+        const size_t ahead = std::min<size_t>(255, avail - (b0 + n));  // look-ahead: a pair that starts here gets its full count
         const size_t n16 = (n + 15) & ~(size_t)15;
         if (d.in.ensure(n + ahead + 16) || d.a.ensure(n16) || d.b.ensure(n16) || d.ws.ensure(rl_encode_workspace_bytes(n))) return -1;
         if (h2d(d, d.in.p, data + b0, n + ahead)) return -1;
@@ -1051,6 +1055,12 @@ int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
     collect_timing(G);
     *pairs = total;
     return FLRL_OK;
+}
+
+int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8_t* counts, uint8_t* values, size_t pair_cap,
+                              size_t* pairs)
+{
+    return flrl_rl_gpu_compress_part_into(data, size, 0, 0, ngpus, counts, values, pair_cap, pairs);
 }
 
 int flrl_rl_gpu_compress(const uint8_t* data, size_t size, int ngpus, uint8_t** counts, uint8_t** values, size_t* pairs)

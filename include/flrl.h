@@ -152,6 +152,12 @@ int flrl_rl_gpu_compress_into(const uint8_t* data, size_t size, int ngpus, uint8
                               size_t* pairs);
 int flrl_rl_gpu_decompress_into(const uint8_t* counts, const uint8_t* values, size_t pairs, int ngpus, uint8_t* out,
                                 size_t out_cap, size_t* out_size);
+/* One PART of a longer stream (what a caller that streams a file through bounded buffers needs; the CLI does): encodes
+ * data[0 .. size), whose counts may look into the `lookahead` bytes behind it (up to 255 are used), given that
+ * `prev_run` bytes equal to data[0] come immediately before data[0].  Part outputs concatenate to the stream's output
+ * (the shard semantics of flrl_rl_encode, through the host layer). */
+int flrl_rl_gpu_compress_part_into(const uint8_t* data, size_t size, size_t lookahead, uint64_t prev_run, int ngpus, uint8_t* counts,
+                                   uint8_t* values, size_t pair_cap, size_t* pairs);
 
 /* ngpus > 1: how shard payloads are concatenated after the NCCL all-gather of their sizes.
  * 0 (default): every GPU copies its payload straight to its offset in the host buffer (8 PCIe links in parallel);
