@@ -63,6 +63,7 @@ void compress(Method method, const char* input, const char* output)
             printGpuTimers("Compression");
         } catch (const std::exception& e) {
             std::cerr << "[ERROR]: " << e.what() << '\n';
+            remove(output);  // no partial container is left behind
         }
         return;
     }
@@ -106,6 +107,7 @@ void decompress(Method method, const char* input, const char* output)
             printGpuTimers("Decompression");
         } catch (const std::exception& e) {
             std::cerr << "[ERROR]: " << e.what() << '\n';
+            remove(output);
         }
         return;
     }

@@ -123,7 +123,7 @@ def test_rl_decode_rejects_malformed(oracle, flrl):
 @pytest.mark.parametrize("mean", [4, 64, 4096])
 def test_rl_full_size_properties(mean, oracle, flrl):
     """BASELINE.json config 3 at full size (1 GiB): device round trip, sum(counts) == n, counts in 1..255, no two
-    adjacent pairs mergeable; a 4 MiB prefix of the pair stream is compared with the oracle."""
+    adjacent pairs mergeable; the whole pair stream is compared with the oracle."""
     import torch
 
     import bench
@@ -140,8 +140,7 @@ def test_rl_full_size_properties(mean, oracle, flrl):
     dec = flrl.RLDecoder(n, counts.numel())
     dec.launch(counts, values)
     assert torch.equal(dec.result(), d_in)
-    m = 4 << 20
-    c_ref, v_ref = oracle.rl_compress(d_in[:m].cpu().numpy())
-    k = c_ref.size - 1  # the prefix's last pair may continue past the cut
-    assert np.array_equal(counts[:k].cpu().numpy(), c_ref[:k])
-    assert np.array_equal(values[:k].cpu().numpy(), v_ref[:k])
+    c_ref, v_ref = oracle.rl_compress(d_in.cpu().numpy())  # EVERY pair against the oracle (the C port: seconds per GiB)
+    assert counts.numel() == c_ref.size
+    assert np.array_equal(counts.cpu().numpy(), c_ref)
+    assert np.array_equal(values.cpu().numpy(), v_ref)
