@@ -200,6 +200,7 @@ struct RlePending {               // a tile of this CTA, from "taken" to "stored
     uint32_t first_byte;           // in[tile base]: the value of the run that enters the tile
     long long tile;
     uint64_t g0;                   // first pair slot of the tile (the scanner's answer)
+    uint32_t skip;                 // 1: more boundaries than the ring holds — the tile is left to the second pass
     // written by the service warp BEFORE it posts the tile's pair count: whoever sees the scanner's answer sees these
     uint32_t tot;                  // pairs of the tile (staged + nl)
     uint32_t nl;                   // emitted pairs that start at 255-splits before the tile's first run start
@@ -207,6 +208,7 @@ struct RlePending {               // a tile of this CTA, from "taken" to "stored
     uint32_t lead_first;           // tile-relative position of the first such split
     uint32_t first_start;          // tile-relative position of the tile's first run start (RL_TILE if none)
     uint32_t lagged;               // count of the last pair before the tile; 0 = not ours to write
+    uint32_t posted;               // tile's sequence number + 1 in this CTA once the six words above are written
 };
 
 struct RleMeta {                   // compute warps -> service warp, per tile
@@ -250,6 +252,7 @@ __device__ __noinline__ void rle_store_tile(uint32_t qi, uint8_t* __restrict__ c
                                             uint64_t* __restrict__ d_pairs, long long tiles, int tid, int nthr)
 {
     const RlePending& e = rle_shared().q[qi];
+    if (e.skip) return;  // nothing of it is written here: the second pass does the whole tile
     const uint32_t nl = e.nl;
     const uint64_t g0 = e.g0;
     if (tid == 0) {
@@ -275,8 +278,16 @@ __global__ void __launch_bounds__(RLE_THREADS, RLE_CTAS_PER_SM)
 rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __restrict__ in, size_t n, size_t n_avail, size_t n_scan,
                  uint32_t prev_phase, int has_prev, uint8_t* __restrict__ counts, uint8_t* __restrict__ values, size_t pair_cap,
                  uint64_t* __restrict__ d_pairs, uint64_t* __restrict__ d1, uint64_t* __restrict__ inc, uint32_t* __restrict__ agg,
-                 uint32_t* __restrict__ next_tile, uint32_t* __restrict__ role, long long tiles)
+                 uint32_t* __restrict__ next_tile, uint32_t* __restrict__ role, uint32_t* __restrict__ redo, long long tiles, int pass)
 {
+    // pass 0: every tile; a tile with more pair boundaries than the ring of staged pairs holds is only COUNTED (its pairs
+    // take part in the scan) and put on the `redo` list.  pass 1 (a second launch, right behind): the tiles of that list,
+    // with every first slot and every run start already final, written directly in rounds of one ring.  Nothing ever
+    // waits for its own first slot while it holds a tile other tiles wait for: dense input (random bytes: 16384 pairs
+    // per tile) costs a second read of those tiles, not a serialised grid (measured before: 170 ms per GiB).
+    uint32_t* const redo_n = role + 1;     // pass 0: tiles on the list; pass 1: read only
+    uint32_t* const redo_next = role + 2;  // pass 1: next list entry to take
+    if (pass && *redo_n == 0) return;      // the usual case: nothing was left over
     uint8_t* const inb = rle_smem();                   // swizzled tile buffers
     uint8_t* const val8 = rle_val8();                  // ring of staged values
     uint8_t* const pos8 = rle_pos8();                  // ring of staged positions (mod 256)
@@ -285,7 +296,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) {
-        sh.role = atomicAdd(role, 1u);
+        sh.role = pass == 0 ? atomicAdd(role, 1u) : 1u;  // the second pass needs no scanner
 #pragma unroll
         for (int b = 0; b < RL_NBUF; ++b) {
 #pragma unroll
@@ -296,6 +307,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         mbar_init(&meta_bar[1], 1);
         mbar_init(&aux, 1);
         fence_mbar_init();
+        for (int i = 0; i < RLE_Q; ++i) sh.q[i].posted = 0;
     }
     __syncthreads();
     if (sh.role == 0) {  // the first CTA that runs is the scanner
@@ -367,11 +379,17 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         // One id per atomic, also at the start: a CTA that held two CONSECUTIVE ids would make the next CTA's tile wait
         // (for its first slot) until this CTA has finished a whole tile and counted the second one, and so on down the
         // grid — measured: tiles with more pairs than the ring holds then run one after the other (170 ms per GiB).
+        const uint32_t n_redo = pass ? *redo_n : 0u;
+        auto take = [&]() -> long long {  // lane 0: the next tile id (>= tiles: none left)
+            if (pass == 0) return (long long)atomicAdd(next_tile, 1u);
+            const uint32_t i = atomicAdd(redo_next, 1u);
+            return i < n_redo ? (long long)redo[i] : tiles;
+        };
         long long cur = 0, nxt = 0, nxt2 = 0;
-        if (lane == 0) cur = atomicAdd(next_tile, 1u);
+        if (lane == 0) cur = take();
         cur = __shfl_sync(0xffffffffu, cur, 0);
         start_tile(cur, 0);
-        if (lane == 0) nxt = atomicAdd(next_tile, 1u);
+        if (lane == 0) nxt = take();
         nxt = __shfl_sync(0xffffffffu, nxt, 0);
         for (uint32_t k = 0;; ++k) {
             const long long tile = cur;
@@ -413,12 +431,13 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                 // tile (it cannot know where the next boundary is); a boundary at or past n is not a pair
                 e.lagged = (tile > 0 && BpB < n + RL_BIAS) ? lagged : 0u;
                 __threadfence_block();  // ... before the post: the scanner's answer implies the six words above
-                st_relaxed_u32(agg + tile, 0x80000000u | tot);  // to the scanner
+                *reinterpret_cast<volatile uint32_t*>(&e.posted) = k + 1u;
+                if (pass == 0) st_relaxed_u32(agg + tile, 0x80000000u | tot);  // to the scanner
             }
             __syncwarp();
             // the id of this CTA's tile k+2, taken as late as possible (tiles should start in id order: a tile's first slot
             // waits for every earlier tile) yet early enough that the atomic's round trip hides behind the next wait
-            if (lane == 0) nxt2 = atomicAdd(next_tile, 1u);
+            if (lane == 0) nxt2 = take();
             if (RL_NBUF == 1) {
                 mbar_wait_sleep(&freeb[0], k & 1u);  // the compute warps are done with the tile: the buffer takes the next one
                 start_tile(nxt, 0);
@@ -449,6 +468,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         if (tid == 0) {
             for (uint32_t i = n_stored; i < need; ++i) {
                 uint64_t g;
+                while (*reinterpret_cast<volatile uint32_t*>(&sh.q[i % RLE_Q].posted) != i + 1u) __nanosleep(50);
                 while (!((g = ld_relaxed_u64(inc + sh.q[i % RLE_Q].tile)) >> 63)) __nanosleep(50);
                 sh.q[i % RLE_Q].g0 = g & ~(1ull << 63);
             }
@@ -629,7 +649,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
 
         // ---- compaction: value and position of every boundary into the ring
         const uint32_t wbyte = buf[warp * RL_WSPAN];  // value of the run that enters the warp's rows
-        if (total_all <= (uint32_t)RL_RING) {
+        if (pass == 0 && total_all <= (uint32_t)RL_RING) {
             // room in the ring?  (the oldest waiting tile's boundaries start at its `head`)
             if (n_stored < k && ring_head + total_all - sh.q[n_stored % RLE_Q].head > (uint32_t)RL_RING) {
                 do {
@@ -666,16 +686,29 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             if (tid == 0) {
                 me.head = ring_head;
                 me.total = total_emit;
+                me.skip = 0;
             }
             ring_head += total_all;
             __syncwarp();
             if (lane == 0) mbar_arrive(&freeb[buf_i]);  // the tile buffer may be refilled
             while (n_stored < upto) store_tile_light(n_stored++, k);
+        } else if (pass == 0) {
+            // more boundaries than the ring holds: counted (the service warp posts it like any tile), left to the second pass
+            if (tid == 0) {
+                me.head = ring_head;
+                me.total = 0;
+                me.skip = 1;
+                redo[atomicAdd(redo_n, 1u)] = (uint32_t)tile;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&freeb[buf_i]);
+            while (n_stored < upto) store_tile_light(n_stored++, k);
         } else {
-            // rare: more boundaries than the ring holds -> written at once, in rounds, after everything that waits
+            // second pass: the tile's first slot is final; its pairs are written at once, in rounds of one ring
             if (tid == 0) {
                 me.head = 0;
                 me.total = 0;
+                me.skip = 0;
             }
             bar_sync(BAR_COMPUTE, RL_THREADS);  // me.* is written
             wait_slots(k + 1u);
@@ -694,9 +727,11 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                     }
                 }
                 uint32_t q = rel0 - w0;
+                // rows whose boundaries all lie outside this round's window have nothing to stage
+                const bool mine = rel0 <= w0 + (uint32_t)RL_RING && rel0 + (packed & 0xffffu) > w0;
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
-                    uint32_t bits = M[g];
+                    uint32_t bits = mine ? M[g] : 0u;
                     while (bits) {
                         const uint32_t p = 32u * g + (uint32_t)__ffs(bits) - 1u;
                         bits &= bits - 1;
@@ -766,6 +801,7 @@ cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint
     uint32_t* agg = reinterpret_cast<uint32_t*>(inc + tmax);  // pair counts (tiles -> scanner)
     uint32_t* next_tile = agg + tmax;                   // tile counter
     uint32_t* role = next_tile + 1;                     // role counter: the first CTA that runs is the scanner
+    uint32_t* redo = next_tile + 4;                     // [+2] tiles left to the second pass, [+3] its counter, then the list
     cudaError_t e = cudaMemsetAsync(d_ws, 0, rl_encode_workspace_bytes(n), stream);
     if (e != cudaSuccess) return e;
     // the input as rows of 128 bytes; the partial last row is loaded with plain loads
@@ -804,9 +840,10 @@ cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint
     }
     // one CTA becomes the scanner, the others take tiles; CTAs that are not resident at once simply start later
     const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap - 1) + 1;
-    rl_encode_kernel<<<grid, RLE_THREADS, RLE_SMEM, stream>>>(tmap, d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), prev_run != 0,
-                                                              d_counts, d_values, pair_cap, d_pairs, d1, inc, agg, next_tile, role,
-                                                              (long long)tiles);
+    for (int pass = 0; pass < 2; ++pass)  // the second launch finds its list empty unless tiles had more pairs than the ring holds
+        rl_encode_kernel<<<grid, RLE_THREADS, RLE_SMEM, stream>>>(tmap, d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), prev_run != 0,
+                                                                  d_counts, d_values, pair_cap, d_pairs, d1, inc, agg, next_tile, role, redo,
+                                                                  (long long)tiles, pass);
     return cudaGetLastError();
 }
 
