@@ -1,18 +1,19 @@
-// fl_decode.cu — fixed-length decoder for sm_100a: persistent CTAs, contiguous ranges, TMA pipeline.
+// fl_decode.cu — fixed-length decoder for sm_100a: offsets pre-pass, then persistent CTAs over a moving window of tiles.
 //
 // Replaces compressInitializeFrameStartIndiciesBits + thrust::exclusive_scan + decompressCalculateOutput
 // (/root/reference/src/fl/fl_gpu.cu:687-698, :805-808, :728-755) with one launch.
 //
-// Where a frame's values start depends only on the widths array (N/128 bytes), not on the payload,
-// so no per-tile look-back is needed:
-//   * grid = 2 CTAs per SM (all co-resident); CTA c owns a CONTIGUOUS range of 128-frame tiles;
-//   * phase 0: the CTA sums the widths of its range (a few tens of KiB, coalesced 16-byte loads),
-//     publishes the sum and reads its predecessors' sums once (one look-back per CTA, not per tile);
-//   * phase 1: a producer warp walks the range with a running offset: one 512-byte coalesced load
-//     brings the widths of 4 tiles, a segmented warp scan gives every frame's offset, and for each
-//     tile one TMA bulk copy of exactly its 16*sum(b) value bytes is issued into a ring of
-//     FLD_STAGES shared-memory stages (full / free mbarriers) — several tiles are always in flight;
-//   * 8 unpack warps wait on the stage's mbarrier, pull their words into registers, unpack lane-locally
+// Where a frame's values start depends only on the widths array (N/128 bytes), not on the payload.  So:
+//   * a small PRE-PASS (fl_tile_offsets_kernel, one thread per 128-frame tile, block scan + one decoupled look-back per
+//     block of 256 tiles) turns the widths into the first value unit of every tile and checks that every width is
+//     1..8; it reads N/128 bytes — 0.5 % of the decoder's traffic — and removes every dependency between tiles;
+//   * the decoder proper is a grid of persistent CTAs (FLD_CTAS per SM) that take tiles c, c + G, c + 2G, ...: all
+//     CTAs together read and write ONE moving window of G consecutive tiles (measured with a plain streaming kernel:
+//     one window beats one contiguous range per CTA, and more, smaller CTAs beat two big ones);
+//   * a producer warp per CTA walks the CTA's tiles: one coalesced load brings the widths of 4 tiles, a segmented
+//     warp scan gives every frame's offset inside its tile, and for each tile one TMA bulk copy of exactly its
+//     16*sum(b) value bytes is issued into a ring of FLD_STAGES shared-memory stages (full / free mbarriers);
+//   * the unpack warps wait on the stage's mbarrier, pull their words into registers, unpack lane-locally
 //     (flrl_bits.cuh), store 2 x 16 bytes per lane (a warp writes 1 KiB of contiguous output per item, no staging
 //     buffer, no store-side synchronisation) and release the stage.
 #include <stdlib.h>
@@ -32,7 +33,7 @@ static constexpr int FLD_TILE_BYTES = FLD_TILE_FRAMES * 128;  // 16 KiB of outpu
                    // 8 = streaming stores (st.cs), 16 = write-through stores (st.wt): none of 1, 4, 8, 16 changes the time
 #endif
 #ifndef FLD_STAGES_N
-#define FLD_STAGES_N 5
+#define FLD_STAGES_N 4
 #endif
 static constexpr int FLD_STAGES = FLD_STAGES_N;
 #ifndef FLD_UNPACK
@@ -43,9 +44,11 @@ static constexpr int FLD_THREADS = FLD_UNPACK_THREADS + 32;   // + producer warp
 static constexpr int FLD_ITEMS = FLD_TILE_BYTES / 32 / FLD_UNPACK_THREADS;  // 32-byte items per thread per tile = 2
 static constexpr int FLD_STAGE_BYTES = FLD_TILE_BYTES + 128;  // slack for the unpacker's over-reads
 #ifndef FLD_CTAS
-#define FLD_CTAS 2
+#define FLD_CTAS 3
 #endif
 static constexpr int FLD_CTAS_PER_SM = FLD_CTAS;
+
+__device__ __forceinline__ size_t umin64(size_t a, size_t b) { return a < b ? a : b; }
 
 struct __align__(16) FldMeta {
     uint16_t off[FLD_TILE_FRAMES];  // exclusive prefix of widths inside the tile (16-byte units)
@@ -116,24 +119,75 @@ __device__ __noinline__ void decode_tail_frame(const uint8_t* vin, uint32_t avai
     }
 }
 
-__device__ __forceinline__ size_t umin64(size_t a, size_t b) { return a < b ? a : b; }
+// ---- pre-pass: first value unit (16 bytes) of every tile ------------------------------------------
+// tile_base[t] = sum of the widths of all full frames before tile t, t = 0 .. tiles (the last entry is the total);
+// *err = 1 if a width of a full frame is outside 1..8 (widths are clamped to 8 for the sums, as the decoder does).
+static constexpr int FLO_THREADS = 256;
+__global__ void __launch_bounds__(FLO_THREADS) fl_tile_offsets_kernel(const uint8_t* __restrict__ bits, size_t full_frames, long long tiles,
+                                                                      uint64_t* __restrict__ tile_base, uint64_t* __restrict__ desc,
+                                                                      int* __restrict__ err)
+{
+    __shared__ uint32_t wsum[FLO_THREADS / 32];
+    __shared__ uint64_t block_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long t = (long long)blockIdx.x * FLO_THREADS + tid;
+    const bool aligned = (reinterpret_cast<uintptr_t>(bits) & 15) == 0;
+    uint32_t sum = 0;
+    bool bad = false;
+    if (t < tiles) {
+        const size_t f0 = (size_t)t * FLD_TILE_FRAMES;
+#pragma unroll
+        for (int i = 0; i < FLD_TILE_FRAMES; i += 16) {
+            const size_t f = f0 + i;
+            if (f < full_frames) sum += sum_bytes16(clamp_widths(ld_widths16(bits, f, full_frames, aligned), (int)umin64(16, full_frames - f), bad));
+        }
+    }
+    if (bad) atomicExch(err, 1);  // malformed container
+    uint32_t inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    uint32_t wbase = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < FLO_THREADS / 32; ++k) {
+        if (k < warp) wbase += wsum[k];
+        total += wsum[k];
+    }
+    if (warp == 0) {
+        uint64_t base = 0;
+        if (blockIdx.x > 0) {
+            if (lane == 0) st_relaxed_u64(desc + blockIdx.x, LB_AGG | total);
+            base = lookback_sum64(desc, (int)blockIdx.x, lane);
+        }
+        if (lane == 0) {
+            st_relaxed_u64(desc + blockIdx.x, LB_INC | (base + total));
+            block_base = base;
+        }
+    }
+    __syncthreads();
+    if (t < tiles) {
+        const uint64_t excl = block_base + wbase + (inc - sum);
+        tile_base[t] = excl;
+        if (t == tiles - 1) tile_base[tiles] = excl + sum;
+    }
+}
 
 __global__ void __launch_bounds__(FLD_THREADS, FLD_CTAS_PER_SM)
 fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t* __restrict__ values, size_t nvalues,
-                 uint8_t* __restrict__ out, size_t n, uint64_t* __restrict__ desc, int* __restrict__ err, long long tiles)
+                 uint8_t* __restrict__ out, size_t n, const uint64_t* __restrict__ tile_base, int* __restrict__ err, long long tiles)
 {
     extern __shared__ __align__(128) uint8_t smem[];  // FLD_STAGES x FLD_STAGE_BYTES
     __shared__ FldMeta meta[FLD_STAGES];
     __shared__ __align__(8) uint64_t full[FLD_STAGES], freeb[FLD_STAGES];
-    __shared__ uint32_t wsum[FLD_THREADS / 32];
-    __shared__ uint64_t range_end;  // value offset (16-byte units) after the CTA's last full frame
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long G = gridDim.x, c = blockIdx.x;
-    const long long t0 = tiles * c / G, t1 = tiles * (c + 1) / G, T = t1 - t0;
+    const long long T = (tiles - c + G - 1) / G;  // this CTA's tiles: c, c + G, c + 2G, ...
     const size_t full_frames = n / FRAME;
-    const size_t fbeg = (size_t)t0 * FLD_TILE_FRAMES;
-    const size_t fend = umin64((size_t)t1 * FLD_TILE_FRAMES, full_frames);
     const bool aligned = (reinterpret_cast<uintptr_t>(bits) & 15) == 0;
 
     if (tid == 0) {
@@ -143,47 +197,33 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
         }
         fence_mbar_init();
     }
-    // ---- phase 0: sum of the widths of the range ------------------------------------------------
-    {
-        uint32_t acc = 0;
-        bool bad = false;
-        for (size_t f = fbeg + (size_t)tid * 16; f < fend; f += (size_t)FLD_THREADS * 16) {
-            const uint4 q = clamp_widths(ld_widths16(bits, f, fend, aligned), (int)umin64(16, fend - f), bad);
-            acc += sum_bytes16(q);
-        }
-        if (bad) atomicExch(err, 1);  // a width outside 1..8: malformed container
-        acc = __reduce_add_sync(0xffffffffu, acc);
-        if (lane == 0) wsum[warp] = acc;
-    }
     __syncthreads();
 
     if (warp == FLD_UNPACK_THREADS / 32) {
         // =============================== producer warp =====================================
-        uint64_t total = 0;
-#pragma unroll
-        for (int k = 0; k < FLD_THREADS / 32; ++k) total += wsum[k];
-        uint64_t base = 0;
-        if (c > 0) {
-            if (lane == 0) st_relaxed_u64(desc + c, LB_AGG | total);
-            base = lookback_sum64(desc, (int)c, lane);
-        }
-        if (lane == 0) {
-            st_relaxed_u64(desc + c, LB_INC | (base + total));
-            range_end = base + total;
-        }
         const uint64_t nv16 = nvalues / 16;
         const int sub = lane >> 3, part = lane & 7;
-        auto load_batch = [&](long long kb) -> uint4 {
+        // widths of the 16 frames this lane scans in batch kb (tile 4 kb + sub of the CTA's list) and the tile's first value unit
+        auto load_batch = [&](long long kb, uint64_t* tb) -> uint4 {
             const long long k = 4 * kb + sub;
-            return k < T ? ld_widths16(bits, (size_t)(t0 + k) * FLD_TILE_FRAMES + part * 16, fend, aligned) : make_uint4(0, 0, 0, 0);
+            if (k >= T) {
+                *tb = 0;
+                return make_uint4(0, 0, 0, 0);
+            }
+            const long long tile = c + k * G;
+            *tb = tile_base[tile];
+            return ld_widths16(bits, (size_t)tile * FLD_TILE_FRAMES + part * 16, full_frames, aligned);
         };
-        uint4 qn = load_batch(0);
+        uint64_t tbn = 0;
+        uint4 qn = load_batch(0, &tbn);
         for (long long kb = 0; 4 * kb < T; ++kb) {
             uint4 q = qn;
-            qn = load_batch(kb + 1);  // widths of the next 4 tiles are in flight while these are issued
-            const size_t f = (size_t)(t0 + 4 * kb + sub) * FLD_TILE_FRAMES + part * 16;
-            bool bad = false;
-            q = clamp_widths(q, f < fend ? (int)umin64(16, fend - f) : 0, bad);
+            const uint64_t tb = tbn;
+            qn = load_batch(kb + 1, &tbn);  // widths of the next 4 tiles are in flight while these are issued
+            const long long ktile = 4 * kb + sub < T ? c + (4 * kb + sub) * G : tiles;
+            const size_t f = (size_t)ktile * FLD_TILE_FRAMES + part * 16;
+            bool bad = false;  // reported by the pre-pass; here the widths are only clamped
+            q = clamp_widths(q, f < full_frames ? (int)umin64(16, full_frames - f) : 0, bad);
             const uint32_t s16 = sum_bytes16(q);
             uint32_t inc = s16;
 #pragma unroll
@@ -213,6 +253,7 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
                     reinterpret_cast<uint4*>(meta[s].off)[2 * part + 1] = make_uint4(o16[4], o16[5], o16[6], o16[7]);
                 }
                 const uint32_t tot = __shfl_sync(0xffffffffu, inc, 8 * s2 + 7);
+                const uint64_t base = __shfl_sync(0xffffffffu, tb, 8 * s2);
                 __syncwarp();
                 if (lane == 0) {
                     uint64_t units = tot;
@@ -227,7 +268,6 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
                         mbar_arrive(&full[s]);
                     }
                 }
-                base += tot;
             }
         }
     } else {
@@ -250,7 +290,7 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
 #pragma unroll
                 for (int j = 0; j < 5; ++j) g[i][j] = w[q + j];
             }
-            uint8_t* otile = out + (size_t)(t0 + k) * FLD_TILE_BYTES;
+            uint8_t* otile = out + (size_t)(c + k * G) * FLD_TILE_BYTES;
 #pragma unroll
             for (int i = 0; i < FLD_ITEMS; ++i) {
                 const int fr = i * (FLD_UNPACK_THREADS / 4) + (tid >> 2);
@@ -288,12 +328,11 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
             if (lane == 0) mbar_arrive(&freeb[s]);
         }
     }
-    // ---- the CTA of the last range: the final partial frame ---------------------------------------
-    if (c != G - 1) return;
-    __syncthreads();
+    // ---- the first CTA: the final partial frame ----------------------------------------------------
+    if (c != 0) return;
     const uint32_t tail = (uint32_t)(n % FRAME);
     if (tail && nframes == full_frames + 1) {
-        const uint64_t off = range_end * 16;
+        const uint64_t off = tile_base[tiles] * 16;  // value bytes of all full frames
         const uint32_t b = bits[full_frames];
         const uint64_t avail = nvalues > off ? nvalues - off : 0;
         if (b == 0 || b > 8 || ((uint64_t)tail * b + 7) / 8 > avail) {
@@ -327,14 +366,18 @@ cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_
         if (e != cudaSuccess) return e;
         if (dev < 64) sm_count[dev] = sms;
     }
-    const int per_sm = FLD_CTAS_PER_SM;
-    const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)sms * per_sm);
-    uint64_t* desc = reinterpret_cast<uint64_t*>(d_ws);
-    int* err = reinterpret_cast<int*>(desc + tiles);
-    e = cudaMemsetAsync(desc, 0, grid * sizeof(uint64_t), stream);
-    if (e != cudaSuccess) return e;
+    // workspace: [status word][tile_base: tiles + 1 words][look-back descriptors of the pre-pass: one per 256 tiles]
+    uint64_t* ws = reinterpret_cast<uint64_t*>(d_ws);
+    int* err = reinterpret_cast<int*>(ws + tiles);
+    uint64_t* tile_base = ws + tiles + 1;
+    uint64_t* desc = tile_base + tiles + 1;
+    const unsigned oblocks = (unsigned)((tiles + FLO_THREADS - 1) / FLO_THREADS);
     e = cudaMemsetAsync(err, 0, sizeof(uint64_t), stream);
     if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(desc, 0, oblocks * sizeof(uint64_t), stream);
+    if (e != cudaSuccess) return e;
+    fl_tile_offsets_kernel<<<oblocks, FLO_THREADS, 0, stream>>>(d_bits, n / FRAME, (long long)tiles, tile_base, desc, err);
+    const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)sms * FLD_CTAS_PER_SM);
     constexpr int smem = FLD_STAGES * FLD_STAGE_BYTES;
     static bool done[64];
     if (!(dev < 64 && done[dev])) {
@@ -342,7 +385,7 @@ cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_
         if (e != cudaSuccess) return e;
         if (dev < 64) done[dev] = true;
     }
-    fl_decode_kernel<<<grid, FLD_THREADS, smem, stream>>>(d_bits, nframes, d_values, nvalues, d_out, n, desc, err, (long long)tiles);
+    fl_decode_kernel<<<grid, FLD_THREADS, smem, stream>>>(d_bits, nframes, d_values, nvalues, d_out, n, tile_base, err, (long long)tiles);
     return cudaGetLastError();
 }
 

@@ -137,7 +137,12 @@ fl_encode_kernel(const uint8_t* __restrict__ in, size_t n, uint8_t* __restrict__
     __shared__ uint32_t tail_scratch[36];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (blockIdx.x == 0) {  // the scanner CTA
+    // the first CTA that RUNS is the grid's scanner (role counter next to the tile counter): nothing depends on which
+    // CTA the hardware places first, nor on the whole grid being resident at once
+    __shared__ uint32_t scanner_role;
+    if (tid == 0) scanner_role = atomicAdd(next_tile + 2, 1u);
+    __syncthreads();
+    if (scanner_role == 0) {
         if (warp == 0) scan_pair_counts(agg, inc, tiles, lane);
         return;
     }

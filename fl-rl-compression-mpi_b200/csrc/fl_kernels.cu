@@ -22,8 +22,12 @@ size_t fl_tiles(size_t n)
 }
 
 size_t fl_encode_workspace_bytes(size_t n);  // fl_encode.cu
-// one workspace serves both directions: the decoder's look-back descriptors (1 word per tile) + status, or the encoder's
-// scanner arrays
-size_t fl_workspace_bytes(size_t n) { return std::max((fl_tiles(n) + 4) * sizeof(uint64_t) + 16, fl_encode_workspace_bytes(n)); }
+// one workspace serves both directions: the decoder's status word at [tiles] (fl_decode_status), the first value unit of
+// every tile and the pre-pass's look-back descriptors behind it, or the encoder's scanner arrays
+size_t fl_workspace_bytes(size_t n)
+{
+    const size_t t = fl_tiles(n);
+    return std::max((2 * t + t / 256 + 8) * sizeof(uint64_t) + 16, fl_encode_workspace_bytes(n));
+}
 
 }  // namespace flrl

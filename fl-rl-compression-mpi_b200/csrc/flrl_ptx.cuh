@@ -68,13 +68,7 @@ __device__ __forceinline__ void tma_prefetch_l2(const void* gsrc, uint32_t bytes
 {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
 }
-// shared -> global bulk copy (bulk async-group completion)
-__device__ __forceinline__ void tma_store_1d(void* gdst, const void* smem_src, uint32_t bytes)
-{
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
-                 "r"(bytes)
-                 : "memory");
-}
+// shared -> global bulk copies complete in bulk async-groups
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // L2 eviction-priority policies for the bulk copies
 __device__ __forceinline__ uint64_t l2_policy_evict_first()
@@ -108,11 +102,6 @@ __device__ __forceinline__ void tma_store_wait_read()
 {
     asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
-template <int N>
-__device__ __forceinline__ void tma_store_wait()
-{
-    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
-}
 // make generic-proxy shared-memory writes visible to the async proxy (TMA store source)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -121,16 +110,6 @@ __device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p)
     uint64_t v;
     asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
-}
-__device__ __forceinline__ uint64_t ld_acquire_u64(const uint64_t* p)
-{
-    uint64_t v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_u64(uint64_t* p, uint64_t v)
-{
-    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v)
 {

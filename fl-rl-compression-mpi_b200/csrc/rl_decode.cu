@@ -68,7 +68,12 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
     __shared__ uint64_t obase_s[2];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (blockIdx.x == 0) {  // the scanner CTA
+    // the first CTA that RUNS is the grid's scanner (role counter next to the tile counter): nothing depends on which
+    // CTA the hardware places first, nor on the whole grid being resident at once
+    __shared__ uint32_t scanner_role;
+    if (tid == 0) scanner_role = atomicAdd(next_tile + 2, 1u);
+    __syncthreads();
+    if (scanner_role == 0) {
         if (warp == 0) scan_pair_counts(agg, inc, tiles, lane);
         return;
     }
@@ -314,7 +319,7 @@ cudaError_t rl_decode_launch(const uint8_t* d_counts, const uint8_t* d_values, s
     cudaError_t e = cudaMemsetAsync(d_ws, 0, rl_decode_workspace_bytes(pairs), stream);
     if (e != cudaSuccess) return e;
     constexpr int smem = RLD_SLOTS * 2 * RLD_PAIRS + (RLD_PAIRS + 4) * 4 + (RLD_PAIRS + 8) * 2;
-    // the grid must be fully co-resident: the tiles wait for the scanner CTA, the scanner for every tile taken
+    // tiles are taken from a counter by CTAs that run, and the first CTA that runs is the scanner: no co-residency is required
     int dev = 0;
     e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
