@@ -3,12 +3,12 @@
 // The reference documents RL (IMPLEMENTATION-PLAN.md:83-152: mask -> scan -> start indices -> split of
 // runs > 255 -> emit) but ships no code.  Structure here:
 //
-//   * persistent CTAs (4 per SM) take 16 KiB tiles from an atomic counter, so tile order is time order:
+//   * persistent CTAs (6 per SM) take 16 KiB tiles from an atomic counter, so tile order is time order:
 //     everything a tile depends on was started earlier, by a CTA that never waits for a later tile.  The CTA
 //     that runs first becomes the grid's scanner (role counter), so nothing depends on CTA placement or on
 //     the whole grid being resident;
 //   * a tile is 128 ROWS of 128 bytes, loaded by TMA as a 2-D tensor with the 128-byte swizzle (four boxes of
-//     32 rows, one mbarrier each, two tile buffers per CTA so the next tile lands while this one is worked on):
+//     32 rows, one mbarrier each; one tile buffer per CTA — measured: six CTAs with one buffer beat four with two):
 //     a thread owns one row and reads it with eight conflict-free LDS.128 (16-byte piece j of row r sits at
 //     piece j ^ (r & 7)); a warp owns 4 KiB of consecutive bytes;
 //   * per row: run-start bit mask of its 128 bytes (XOR with the byte-shifted word, SWAR non-zero-byte test,
@@ -47,16 +47,24 @@
 
 namespace flrl {
 
-static constexpr int RL_WARPS = 4;                      // compute warps
-static constexpr int RL_THREADS = RL_WARPS * 32;        // compute threads = rows per tile
-static constexpr int RLE_THREADS = RL_THREADS + 32;     // + service warp
-static constexpr int RL_ROW = 128;                      // bytes per thread and tile (the swizzle span)
-static constexpr int RL_TILE = RL_ROW * RL_THREADS;     // 16 KiB
-static constexpr int RL_WSPAN = RL_TILE / RL_WARPS;     // 4 KiB of consecutive bytes per warp = one TMA box of 32 rows
-#ifndef RL_NBUF_N
-#define RL_NBUF_N 2
+#ifndef RL_SEG_N
+#define RL_SEG_N 128
 #endif
-static constexpr int RL_NBUF = RL_NBUF_N;               // tile buffers per CTA (2: the next tile lands while this one is worked on)
+static constexpr int RL_ROW = 128;                      // bytes per row of the tile (the swizzle span)
+static constexpr int RL_ROWS = 128;                     // rows per tile
+static constexpr int RL_TILE = RL_ROW * RL_ROWS;        // 16 KiB
+static constexpr int RL_BOXES = 4;                      // TMA boxes per tile
+static constexpr int RL_BOX = RL_TILE / RL_BOXES;       // 4 KiB = 32 rows
+static constexpr int RL_SEG = RL_SEG_N;                 // consecutive bytes per compute thread and tile: a row (128) or half a row (64)
+static constexpr int RL_NW = RL_SEG / 32;               // 32-bit mask words per thread
+static constexpr int RL_THREADS = RL_TILE / RL_SEG;     // compute threads
+static constexpr int RL_WARPS = RL_THREADS / 32;        // compute warps
+static constexpr int RLE_THREADS = RL_THREADS + 32;     // + service warp
+static constexpr int RL_WSPAN = 32 * RL_SEG;            // consecutive bytes per warp
+#ifndef RL_NBUF_N
+#define RL_NBUF_N 1
+#endif
+static constexpr int RL_NBUF = RL_NBUF_N;               // tile buffers per CTA (2: the next tile lands while this one is worked on; 4 CTAs per SM then)
 #ifndef RL_RING_PAIRS
 #define RL_RING_PAIRS 8192
 #endif
@@ -68,7 +76,7 @@ static constexpr int RL_NBUF = RL_NBUF_N;               // tile buffers per CTA 
 #define RLE_PF_LEAD 0  // tiles between a load and an L2 prefetch issued with it (0: none; measured: no gain with two buffers)
 #endif
 #ifndef RLE_CTAS
-#define RLE_CTAS 4
+#define RLE_CTAS 6
 #endif
 static constexpr int RL_RING = RL_RING_PAIRS;           // staged pairs (power of two)
 static constexpr int RL_RINGB = RL_RING + 32;           // + mirror of entry 0 + over-read slack of the unaligned 16-byte reads
@@ -77,7 +85,7 @@ static constexpr int RLE_CTAS_PER_SM = RLE_CTAS;
 static constexpr uint64_t RL_BIAS = 255;                // run starts are stored as S + 255 >= 0
 static constexpr uint32_t BAR_COMPUTE = 1;              // named barrier of the compute warps
 static_assert((RL_RING & (RL_RING - 1)) == 0 && RL_RING >= 512, "ring indices are masked");
-static_assert(RL_ROW == 128 && RL_WSPAN == 32 * RL_ROW, "one row per lane, one 32-row box per warp");
+static_assert(RL_ROW == 128 && (RL_SEG == 128 || RL_SEG == 64) && RL_BOX % RL_WSPAN == 0, "a thread owns a row or half a row; a warp stays inside one box");
 
 // ---- run-start flags of 32 consecutive bytes -------------------------------------------------
 // bit (4k + j) of the result: byte j of word k differs from the byte before it.
@@ -287,12 +295,17 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
     // per tile) costs a second read of those tiles, not a serialised grid (measured before: 170 ms per GiB).
     uint32_t* const redo_n = role + 1;     // pass 0: tiles on the list; pass 1: read only
     uint32_t* const redo_next = role + 2;  // pass 1: next list entry to take
-    if (pass && *redo_n == 0) return;      // the usual case: nothing was left over
+    if (pass) {
+        // launched with programmatic stream serialization: the launch itself overlaps the first pass; its results are
+        // visible after this wait
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        if (*reinterpret_cast<volatile uint32_t*>(redo_n) == 0) return;  // the usual case: nothing was left over
+    }
     uint8_t* const inb = rle_smem();                   // swizzled tile buffers
     uint8_t* const val8 = rle_val8();                  // ring of staged values
     uint8_t* const pos8 = rle_pos8();                  // ring of staged positions (mod 256)
     RleShared& sh = rle_shared();
-    __shared__ __align__(8) uint64_t full[RL_NBUF][RL_WARPS], freeb[RL_NBUF], meta_bar[2], aux;
+    __shared__ __align__(8) uint64_t full[RL_NBUF][RL_BOXES], freeb[RL_NBUF], meta_bar[2], aux;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) {
@@ -300,7 +313,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
 #pragma unroll
         for (int b = 0; b < RL_NBUF; ++b) {
 #pragma unroll
-            for (int s = 0; s < RL_WARPS; ++s) mbar_init(&full[b][s], 1);
+            for (int s = 0; s < RL_BOXES; ++s) mbar_init(&full[b][s], 1);
             mbar_init(&freeb[b], RL_WARPS);
         }
         mbar_init(&meta_bar[0], 1);
@@ -326,28 +339,28 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             if (tile >= tiles) {
                 if (lane == 0) sh.cur_tile[b] = -1;
                 __syncwarp();
-                if (lane < RL_WARPS) mbar_arrive(&full[b][lane]);
+                if (lane < RL_BOXES) mbar_arrive(&full[b][lane]);
                 return;
             }
             uint8_t* const buf = inb + b * RL_TILE;
             const size_t tbase = (size_t)tile * RL_TILE;
-            const long long row0 = tile * RL_THREADS;
+            const long long row0 = tile * RL_ROWS;
             if (lane == 0) sh.cur_tile[b] = tile;
             __syncwarp();
             // the box that holds the partial last row of the data (at most one per shard) goes through `aux`
-            const bool tail_here = tail_bytes != 0 && rows_full >= row0 && rows_full < row0 + RL_THREADS;
+            const bool tail_here = tail_bytes != 0 && rows_full >= row0 && rows_full < row0 + RL_ROWS;
             const int tail_part = tail_here ? (int)((rows_full - row0) >> 5) : -1;
-            if (lane < RL_WARPS) {
+            if (lane < RL_BOXES) {
                 const bool have = rows_full > row0 + 32 * lane;  // at least one full row in this box (rows past the end read as 0)
                 if (lane == tail_part) {
                     if (have) {
-                        mbar_expect_tx(&aux, RL_WSPAN);
-                        tma_load_rows(buf + lane * RL_WSPAN, &tmap, (int)(row0 + 32 * lane), &aux);
+                        mbar_expect_tx(&aux, RL_BOX);
+                        tma_load_rows(buf + lane * RL_BOX, &tmap, (int)(row0 + 32 * lane), &aux);
                     }
                 } else if (have) {
-                    if (lane == 0) mbar_expect_tx_only(&full[b][0], RL_WSPAN);  // lane 0 arrives below
-                    else mbar_expect_tx(&full[b][lane], RL_WSPAN);
-                    tma_load_rows(buf + lane * RL_WSPAN, &tmap, (int)(row0 + 32 * lane), &full[b][lane]);
+                    if (lane == 0) mbar_expect_tx_only(&full[b][0], RL_BOX);  // lane 0 arrives below
+                    else mbar_expect_tx(&full[b][lane], RL_BOX);
+                    tma_load_rows(buf + lane * RL_BOX, &tmap, (int)(row0 + 32 * lane), &full[b][lane]);
                 } else if (lane != 0) {
                     mbar_arrive(&full[b][lane]);
                 }
@@ -358,8 +371,8 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
 #if RLE_PF_LEAD
                 // make the load of the tile one grid of tiles ahead an L2 hit (somebody else's tile)
                 {
-                    const size_t pb = tbase + (size_t)RLE_PF_LEAD * RL_TILE + (size_t)lane * RL_WSPAN;
-                    const size_t pe = dmin(pb + RL_WSPAN, n_avail & ~(size_t)15);
+                    const size_t pb = tbase + (size_t)RLE_PF_LEAD * RL_TILE + (size_t)lane * RL_BOX;
+                    const size_t pe = dmin(pb + RL_BOX, n_avail & ~(size_t)15);
                     if (pe > pb) tma_prefetch_l2(in + pb, (uint32_t)(pe - pb));
                 }
 #endif
@@ -389,8 +402,10 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         if (lane == 0) cur = take();
         cur = __shfl_sync(0xffffffffu, cur, 0);
         start_tile(cur, 0);
-        if (lane == 0) nxt = take();
-        nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        if (RL_NBUF > 1) {
+            if (lane == 0) nxt = take();
+            nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        }
         for (uint32_t k = 0;; ++k) {
             const long long tile = cur;
             if (tile >= tiles) break;
@@ -438,9 +453,12 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             // the id of this CTA's tile k+2, taken as late as possible (tiles should start in id order: a tile's first slot
             // waits for every earlier tile) yet early enough that the atomic's round trip hides behind the next wait
             if (lane == 0) nxt2 = take();
-            if (RL_NBUF == 1) {
+            if (RL_NBUF == 1) {  // one buffer: the id just taken is the next tile (never hold an id whose load cannot start)
                 mbar_wait_sleep(&freeb[0], k & 1u);  // the compute warps are done with the tile: the buffer takes the next one
+                nxt = __shfl_sync(0xffffffffu, nxt2, 0);
                 start_tile(nxt, 0);
+                cur = nxt;
+                continue;
             }
             cur = nxt;
             nxt = __shfl_sync(0xffffffffu, nxt2, 0);
@@ -450,8 +468,10 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
 
     // ================================= compute warps =======================================
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t sw = (uint32_t)tid & 7u;       // swizzle of this thread's row
-    const int rowstart = tid * RL_ROW;            // tile-relative position of the row
+    const int rowstart = tid * RL_SEG;            // tile-relative position of this thread's bytes (a row or half a row)
+    const uint32_t sw = (uint32_t)(rowstart / RL_ROW) & 7u;          // swizzle of the row they are in
+    const uint32_t chunk0 = (uint32_t)(rowstart % RL_ROW) >> 4;      // first 16-byte piece of the row that is ours
+    const int mybox = rowstart / RL_BOX;
     uint32_t n_stored = 0;   // tiles of this CTA already written to global memory
     uint32_t ring_head = 0;  // ring position after the last staged boundary (not masked)
 
@@ -490,12 +510,12 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             if (n_stored < k) ga = ld_relaxed_u64(inc + sh.q[n_stored % RLE_Q].tile);
             if (n_stored + 1u < k) gb = ld_relaxed_u64(inc + sh.q[(n_stored + 1u) % RLE_Q].tile);
         }
-        if (warp > 0) mbar_wait(&full[buf_i][warp - 1], fpar);  // the last byte of the previous warp's rows
-        mbar_wait(&full[buf_i][warp], fpar);
+        if (mybox > 0) mbar_wait(&full[buf_i][mybox - 1], fpar);  // the byte before the warp's first one may be in the previous box
+        mbar_wait(&full[buf_i][mybox], fpar);
         const long long tile = *reinterpret_cast<const volatile long long*>(&sh.cur_tile[buf_i]);
         if (tile < 0) break;
         const uint8_t* const buf = inb + buf_i * RL_TILE;
-        const uint8_t* const rowp = buf + rowstart;
+        const uint8_t* const rowp = buf + (rowstart / RL_ROW) * RL_ROW;  // the row (128 bytes, swizzled pieces)
         const size_t tbase = (size_t)tile * RL_TILE;
         // tile-relative limits: positions >= rel_emit are not emitted; position rel_scan is a forced boundary (the end
         // of the data, or far enough into the look-ahead that every emitted pair has its count), nothing after it counts
@@ -504,17 +524,18 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         const bool ragged = rel_emit < (uint32_t)RL_TILE || rel_scan < (uint32_t)RL_TILE;
 
         // ---- step A: the row's run-start mask, its 255-split, pair counts; nothing from other warps is needed
-        uint32_t M[4];
+        uint32_t M[RL_NW];
         {
             // the word that ends with the byte before the row (only its top byte is used)
             // ("before" the stream: a byte that differs from in[0] unless a run is open)
-            uint32_t pw = tid > 0    ? *reinterpret_cast<const uint32_t*>(buf + (rowstart - RL_ROW) + (((7u ^ (uint32_t)(tid - 1)) & 7u) << 4) + 12)
+            const uint32_t pp = (uint32_t)(rowstart - 16);  // the piece before ours (tid > 0): row pp / 128, piece (pp % 128) / 16
+            uint32_t pw = tid > 0    ? *reinterpret_cast<const uint32_t*>(buf + (pp / RL_ROW) * RL_ROW + (((((pp % RL_ROW) >> 4) ^ (pp / RL_ROW)) & 7u) << 4) + 12)
                           : tile > 0 ? *reinterpret_cast<const volatile uint32_t*>(&sh.prev16[buf_i][12])
                                      : (uint32_t)(has_prev ? buf[0] : (uint8_t)~buf[0]) << 24;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                const uint4 a = *reinterpret_cast<const uint4*>(rowp + (((2u * g) ^ sw) << 4));
-                const uint4 c = *reinterpret_cast<const uint4*>(rowp + (((2u * g + 1u) ^ sw) << 4));
+            for (int g = 0; g < RL_NW; ++g) {
+                const uint4 a = *reinterpret_cast<const uint4*>(rowp + (((chunk0 + 2u * g) ^ sw) << 4));
+                const uint4 c = *reinterpret_cast<const uint4*>(rowp + (((chunk0 + 2u * g + 1u) ^ sw) << 4));
                 const uint32_t w[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
                 M[g] = start_mask32(w, pw);
                 pw = c.w;
@@ -522,17 +543,18 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         }
         if (ragged) {  // CTA-uniform: only the last tiles see the end of the data
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+            for (int g = 0; g < RL_NW; ++g) {
                 const int kk = (int)rel_scan - (rowstart + 32 * g);
                 if (kk < 0) M[g] = 0;
                 else if (kk < 32) M[g] = (M[g] & ((1u << kk) - 1u)) | (1u << kk);
             }
         }
-        const uint32_t any = M[0] | M[1] | M[2] | M[3];
-        const unsigned bal = __ballot_sync(0xffffffffu, any != 0);
         // bytes of the row that continue the entering run / last run start of the row (tile relative)
-        const unsigned long long mlo = (unsigned long long)M[0] | ((unsigned long long)M[1] << 32), mhi = (unsigned long long)M[2] | ((unsigned long long)M[3] << 32);
-        const int lead = mlo ? __ffsll((long long)mlo) - 1 : mhi ? 63 + __ffsll((long long)mhi) : RL_ROW;
+        const unsigned long long mlo = (unsigned long long)M[0] | ((unsigned long long)M[1] << 32),
+                                 mhi = RL_NW == 4 ? (unsigned long long)M[RL_NW - 2] | ((unsigned long long)M[RL_NW - 1] << 32) : 0ull;
+        const bool any = (mlo | mhi) != 0;
+        const int lead = mlo ? __ffsll((long long)mlo) - 1 : mhi ? 63 + __ffsll((long long)mhi) : RL_SEG;
+        const unsigned bal = __ballot_sync(0xffffffffu, any);
         const int my_last = rowstart + (mhi ? 127 - __clzll((long long)mhi) : 63 - __clzll((long long)mlo));
         const unsigned lower = bal & lt_mask;
         const int S = __shfl_sync(0xffffffffu, my_last, 31 - __clz(lower | 1u));  // nearest run start before the row, if lower != 0
@@ -542,15 +564,15 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             const uint32_t j = 254u - rr;
             if (j < (uint32_t)lead) {
 #pragma unroll
-                for (int g = 0; g < 4; ++g)
+                for (int g = 0; g < RL_NW; ++g)
                     if ((j >> 5) == (uint32_t)g) M[g] |= 1u << (j & 31u);
             }
         }
-        uint32_t packed = __popc(M[0]) + __popc(M[1]) + __popc(M[2]) + __popc(M[3]);  // <= 128; a warp's sum <= 4096
+        uint32_t packed = __popc(M[0]) + __popc(M[1]) + (RL_NW == 4 ? __popc(M[RL_NW - 2]) + __popc(M[RL_NW - 1]) : 0);  // <= 128; a warp's sum <= 4096
         if (ragged) {
             uint32_t ce = 0;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+            for (int g = 0; g < RL_NW; ++g) {
                 const int kk = (int)rel_emit - (rowstart + 32 * g);
                 const uint32_t em = kk <= 0 ? 0u : (kk >= 32 ? ~0u : ((1u << kk) - 1u));
                 ce += __popc(M[g] & em);
@@ -595,11 +617,17 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         uint32_t total_all = 0, total_emit = 0, mybase = 0, mynl = 0, myfirst = 0;
         int F_t, L_t, L_lastwarp;
         {
-            const int4 Fv = *reinterpret_cast<const int4*>(sh.wfirst[kb]);
-            const int4 Lv = *reinterpret_cast<const int4*>(sh.wlast[kb]);
-            const uint4 Cv = *reinterpret_cast<const uint4*>(sh.wcnt[kb]);
-            const int Fa[4] = {Fv.x, Fv.y, Fv.z, Fv.w}, La[4] = {Lv.x, Lv.y, Lv.z, Lv.w};
-            const uint32_t Ca[4] = {Cv.x, Cv.y, Cv.z, Cv.w};
+            int Fa[RL_WARPS], La[RL_WARPS];
+            uint32_t Ca[RL_WARPS];
+#pragma unroll
+            for (int i = 0; i < RL_WARPS; i += 4) {
+                const int4 Fv = *reinterpret_cast<const int4*>(&sh.wfirst[kb][i]);
+                const int4 Lv = *reinterpret_cast<const int4*>(&sh.wlast[kb][i]);
+                const uint4 Cv = *reinterpret_cast<const uint4*>(&sh.wcnt[kb][i]);
+                Fa[i] = Fv.x, Fa[i + 1] = Fv.y, Fa[i + 2] = Fv.z, Fa[i + 3] = Fv.w;
+                La[i] = Lv.x, La[i + 1] = Lv.y, La[i + 2] = Lv.z, La[i + 3] = Lv.w;
+                Ca[i] = Cv.x, Ca[i + 1] = Cv.y, Ca[i + 2] = Cv.z, Ca[i + 3] = Cv.w;
+            }
             int Srun = -1;
 #pragma unroll
             for (int i = 0; i < RL_WARPS; ++i) {
@@ -625,8 +653,9 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                 total_emit += nle_i + (Ca[i] >> 16);
                 if (La[i] >= 0) Srun = La[i];
             }
-            F_t = min(min(Fa[0], Fa[1]), min(Fa[2], Fa[3]));
-            L_t = max(max(La[0], La[1]), max(La[2], La[3]));
+            F_t = Fa[0], L_t = La[0];
+#pragma unroll
+            for (int i = 1; i < RL_WARPS; ++i) F_t = min(F_t, Fa[i]), L_t = max(L_t, La[i]);
             L_lastwarp = La[RL_WARPS - 1];
         }
         RlePending& me = sh.q[k % RLE_Q];
@@ -670,13 +699,13 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             const uint32_t kk0 = wb + mynl + excl;
             uint32_t kk = kk0;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+            for (int g = 0; g < RL_NW; ++g) {
                 uint32_t bits = M[g];
                 while (bits) {
                     const uint32_t p = 32u * g + (uint32_t)__ffs(bits) - 1u;
                     bits &= bits - 1;
                     const uint32_t idx = kk & (RL_RING - 1);
-                    val8[idx] = rowp[((((p >> 4) ^ sw) & 7u) << 4) | (p & 15u)];
+                    val8[idx] = rowp[((((chunk0 + (p >> 4)) ^ sw) & 7u) << 4) | (p & 15u)];
                     pos8[idx] = (uint8_t)(rowstart + p);
                     ++kk;
                 }
@@ -730,13 +759,13 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                 // rows whose boundaries all lie outside this round's window have nothing to stage
                 const bool mine = rel0 <= w0 + (uint32_t)RL_RING && rel0 + (packed & 0xffffu) > w0;
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
+                for (int g = 0; g < RL_NW; ++g) {
                     uint32_t bits = mine ? M[g] : 0u;
                     while (bits) {
                         const uint32_t p = 32u * g + (uint32_t)__ffs(bits) - 1u;
                         bits &= bits - 1;
                         if (q <= (uint32_t)RL_RING) {
-                            val8[q] = rowp[((((p >> 4) ^ sw) & 7u) << 4) | (p & 15u)];
+                            val8[q] = rowp[((((chunk0 + (p >> 4)) ^ sw) & 7u) << 4) | (p & 15u)];
                             pos8[q] = (uint8_t)(rowstart + p);
                         }
                         ++q;
@@ -840,10 +869,25 @@ cudaError_t rl_encode_launch(const uint8_t* d_in, size_t n, size_t n_avail, uint
     }
     // one CTA becomes the scanner, the others take tiles; CTAs that are not resident at once simply start later
     const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)cap - 1) + 1;
-    for (int pass = 0; pass < 2; ++pass)  // the second launch finds its list empty unless tiles had more pairs than the ring holds
-        rl_encode_kernel<<<grid, RLE_THREADS, RLE_SMEM, stream>>>(tmap, d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), prev_run != 0,
-                                                                  d_counts, d_values, pair_cap, d_pairs, d1, inc, agg, next_tile, role, redo,
-                                                                  (long long)tiles, pass);
+    rl_encode_kernel<<<grid, RLE_THREADS, RLE_SMEM, stream>>>(tmap, d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), prev_run != 0, d_counts,
+                                                              d_values, pair_cap, d_pairs, d1, inc, agg, next_tile, role, redo, (long long)tiles, 0);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    // the second pass (it finds its list empty unless tiles had more pairs than the ring holds): launched early
+    // (programmatic dependent launch) so that only its griddepcontrol.wait, not its launch, follows the first pass
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(RLE_THREADS);
+    cfg.dynamicSmemBytes = RLE_SMEM;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, rl_encode_kernel, tmap, d_in, n, n_avail, n_scan, (uint32_t)(prev_run % 255u), (int)(prev_run != 0), d_counts, d_values,
+                           pair_cap, d_pairs, d1, inc, agg, next_tile, role, redo, (long long)tiles, 1);
+    if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 
