@@ -185,22 +185,23 @@ def gen_stream_device(torch, b0, n, seg=1 << 20):
     view = out.view(nseg, seg)
     for kind in range(5):
         first = (kind - s0) % 5
-        c = len(range(first, nseg, 5))
-        if c == 0:
-            continue
-        g = torch.Generator(device="cuda").manual_seed(1000 * (s0 + first) + kind)
-        if kind == 0:
-            batch = torch.zeros(c * seg, dtype=torch.uint8, device="cuda")
-        elif kind == 1:
-            batch = gen_rl_device(torch, c * seg, 4096, seed=7 + s0 + first)
-        elif kind == 2:
-            batch = gen_narrow_device(torch, c * seg, g)
-        elif kind == 3:
-            batch = gen_rl_device(torch, c * seg, 64, seed=11 + s0 + first)
-        else:
-            batch = torch.randint(0, 256, (c * seg,), device="cuda", generator=g, dtype=torch.uint8)
-        view[first::5] = batch.view(c, seg)
-        del batch
+        idx = list(range(first, nseg, 5))
+        for j0 in range(0, len(idx), 2048):  # slabs of at most 2 GiB of one kind: bounds the generators' temporaries
+            sel = idx[j0:j0 + 2048]
+            c = len(sel)
+            g = torch.Generator(device="cuda").manual_seed(1000 * (s0 + sel[0]) + kind)
+            if kind == 0:
+                batch = torch.zeros(c * seg, dtype=torch.uint8, device="cuda")
+            elif kind == 1:
+                batch = gen_rl_device(torch, c * seg, 4096, seed=7 + s0 + sel[0])
+            elif kind == 2:
+                batch = gen_narrow_device(torch, c * seg, g)
+            elif kind == 3:
+                batch = gen_rl_device(torch, c * seg, 64, seed=11 + s0 + sel[0])
+            else:
+                batch = torch.randint(0, 256, (c * seg,), device="cuda", generator=g, dtype=torch.uint8)
+            view[sel[0]:sel[-1] + 1:5] = batch.view(c, seg)
+            del batch
     return out[:n]
 
 

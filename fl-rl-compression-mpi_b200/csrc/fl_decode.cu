@@ -132,16 +132,25 @@ __global__ void __launch_bounds__(FLO_THREADS) fl_tile_offsets_kernel(const uint
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long t = (long long)blockIdx.x * FLO_THREADS + tid;
     const bool aligned = (reinterpret_cast<uintptr_t>(bits) & 15) == 0;
-    uint32_t sum = 0;
+    // a warp reads the widths of its 32 tiles (4 KiB) with coalesced 16-byte loads: in step i lane l holds 16 widths of
+    // tile 4 i + l / 8; the eight partial sums of a tile are added across lanes, and tile j's sum ends up in lane j
+    __shared__ uint32_t tsum[FLO_THREADS];
     bool bad = false;
-    if (t < tiles) {
-        const size_t f0 = (size_t)t * FLD_TILE_FRAMES;
+    {
+        const long long wt0 = (long long)blockIdx.x * FLO_THREADS + warp * 32;  // the warp's first tile
 #pragma unroll
-        for (int i = 0; i < FLD_TILE_FRAMES; i += 16) {
-            const size_t f = f0 + i;
-            if (f < full_frames) sum += sum_bytes16(clamp_widths(ld_widths16(bits, f, full_frames, aligned), (int)umin64(16, full_frames - f), bad));
+        for (int i = 0; i < 8; ++i) {
+            const size_t f = (size_t)wt0 * FLD_TILE_FRAMES + (size_t)(i * 32 + lane) * 16;
+            uint32_t part = 0;
+            if (f < full_frames) part = sum_bytes16(clamp_widths(ld_widths16(bits, f, full_frames, aligned), (int)umin64(16, full_frames - f), bad));
+            part += __shfl_xor_sync(0xffffffffu, part, 1);
+            part += __shfl_xor_sync(0xffffffffu, part, 2);
+            part += __shfl_xor_sync(0xffffffffu, part, 4);
+            if ((lane & 7) == 0) tsum[warp * 32 + 4 * i + (lane >> 3)] = part;
         }
+        __syncwarp();
     }
+    const uint32_t sum = t < tiles ? tsum[tid] : 0u;
     if (bad) atomicExch(err, 1);  // malformed container
     uint32_t inc = sum;
 #pragma unroll
@@ -203,6 +212,9 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
         // =============================== producer warp =====================================
         const uint64_t nv16 = nvalues / 16;
         const int sub = lane >> 3, part = lane & 7;
+        // launched with programmatic stream serialization: everything above overlapped the pre-pass, whose tile_base is
+        // needed (and visible) from here on
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         // widths of the 16 frames this lane scans in batch kb (tile 4 kb + sub of the CTA's list) and the tile's first value unit
         auto load_batch = [&](long long kb, uint64_t* tb) -> uint4 {
             const long long k = 4 * kb + sub;
@@ -330,6 +342,7 @@ fl_decode_kernel(const uint8_t* __restrict__ bits, size_t nframes, const uint8_t
     }
     // ---- the first CTA: the final partial frame ----------------------------------------------------
     if (c != 0) return;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const uint32_t tail = (uint32_t)(n % FRAME);
     if (tail && nframes == full_frames + 1) {
         const uint64_t off = tile_base[tiles] * 16;  // value bytes of all full frames
@@ -366,15 +379,13 @@ cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_
         if (e != cudaSuccess) return e;
         if (dev < 64) sm_count[dev] = sms;
     }
-    // workspace: [status word][tile_base: tiles + 1 words][look-back descriptors of the pre-pass: one per 256 tiles]
+    // workspace: [tiles words unused][status word][look-back descriptors of the pre-pass: one per 256 tiles][tile_base: tiles + 1 words]
     uint64_t* ws = reinterpret_cast<uint64_t*>(d_ws);
     int* err = reinterpret_cast<int*>(ws + tiles);
-    uint64_t* tile_base = ws + tiles + 1;
-    uint64_t* desc = tile_base + tiles + 1;
+    uint64_t* desc = ws + tiles + 1;
     const unsigned oblocks = (unsigned)((tiles + FLO_THREADS - 1) / FLO_THREADS);
-    e = cudaMemsetAsync(err, 0, sizeof(uint64_t), stream);
-    if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(desc, 0, oblocks * sizeof(uint64_t), stream);
+    uint64_t* tile_base = desc + oblocks;
+    e = cudaMemsetAsync(err, 0, (1 + oblocks) * sizeof(uint64_t), stream);  // status word + descriptors, adjacent
     if (e != cudaSuccess) return e;
     fl_tile_offsets_kernel<<<oblocks, FLO_THREADS, 0, stream>>>(d_bits, n / FRAME, (long long)tiles, tile_base, desc, err);
     const unsigned grid = (unsigned)std::min<size_t>(tiles, (size_t)sms * FLD_CTAS_PER_SM);
@@ -385,8 +396,19 @@ cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_
         if (e != cudaSuccess) return e;
         if (dev < 64) done[dev] = true;
     }
-    fl_decode_kernel<<<grid, FLD_THREADS, smem, stream>>>(d_bits, nframes, d_values, nvalues, d_out, n, tile_base, err, (long long)tiles);
-    return cudaGetLastError();
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(FLD_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // the decoder's set-up overlaps the pre-pass
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, fl_decode_kernel, d_bits, nframes, d_values, nvalues, d_out, n, (const uint64_t*)tile_base, err, (long long)tiles);
 }
 
 }  // namespace flrl
