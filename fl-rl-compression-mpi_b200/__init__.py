@@ -35,6 +35,9 @@ lib.flrl_fl_encode.restype = C.c_int
 lib.flrl_fl_encode.argtypes = [_vp, _sz, _vp, _vp, _sz, _vp, _vp, _sz, _vp]
 lib.flrl_fl_decode.restype = C.c_int
 lib.flrl_fl_decode.argtypes = [_vp, _sz, _vp, _sz, _vp, _sz, _vp, _vp, _sz, _vp]
+lib.flrl_fl_decode_static.restype = C.c_int  # no workspace, no allocation (static device scratch inside the library)
+lib.flrl_fl_decode_static.argtypes = [_vp, _sz, _vp, _sz, _vp, _sz, _vp, _vp]
+STATIC_MAX_BYTES = 1 << 30
 
 
 class FlrlError(RuntimeError):

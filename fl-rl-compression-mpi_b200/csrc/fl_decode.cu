@@ -412,3 +412,71 @@ cudaError_t fl_decode_launch(const uint8_t* d_bits, size_t nframes, const uint8_
 }
 
 }  // namespace flrl
+
+// =============================================================================================
+//            flrl_fl_decode_static — the decoder with NO allocation anywhere on its path
+// =============================================================================================
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+// No counterpart in the reference.  The decoder's scratch (status word,
+// look-back descriptors of the pre-pass, first value unit of every tile: 2 words per 16 KiB tile) lives in the
+// file-scope device array below, sized for FLRL_STATIC_MAX_BYTES = 1 GiB of output per call: 1.0 MiB, held by every
+// GPU that loads the library until the process exits.  In host code the array's NAME is a host-side stand-in, not a
+// device address: the address comes from cudaGetSymbolAddress, once per device, with that device current.
+// Every call on a device shares the array, which keeps the last call's contents: fl_decode_launch clears what must start
+// at zero (status word + descriptors) on the caller's stream, everything else is written before it is read.  Calls that
+// OVERLAP on one GPU (two streams) race on it: serialise them, or use flrl_fl_decode with a workspace per call.
+#include <mutex>
+
+#include "abi_common.cuh"
+
+namespace flrl {
+static constexpr size_t FLD_STATIC_TILES = (size_t)FLRL_STATIC_MAX_BYTES / FLD_TILE_BYTES;               // 65536
+static constexpr size_t FLD_STATIC_WORDS = 2 * FLD_STATIC_TILES + FLD_STATIC_TILES / FLO_THREADS + 16;  // what fl_decode_launch lays out
+static __device__ __align__(256) uint64_t g_fld_static_scratch[FLD_STATIC_WORDS];
+}  // namespace flrl
+
+extern "C" int flrl_fl_decode_static(const uint8_t* d_bits, size_t nbits, const uint8_t* d_values, size_t nvalues, uint8_t* d_out, size_t n,
+                                     int* d_status, flrl_stream_t stream)
+{
+    using namespace flrl;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (n > (size_t)FLRL_STATIC_MAX_BYTES)
+        return fail(FLRL_E_CAPACITY, "flrl_fl_decode_static: n = %zu exceeds FLRL_STATIC_MAX_BYTES = %zu (the static scratch is sized for that)", n,
+                    (size_t)FLRL_STATIC_MAX_BYTES);
+    if (n == 0) {
+        if (d_status) {
+            cudaError_t e = cudaMemsetAsync(d_status, 0, sizeof(int), s);
+            if (e != cudaSuccess) return fail_cuda(e, "flrl_fl_decode_static/memset");
+        }
+        return FLRL_OK;
+    }
+    if (!d_bits || !d_values || !d_out) return fail(FLRL_E_ARG, "flrl_fl_decode_static: NULL buffer");
+    if (nbits != (n + FRAME - 1) / FRAME) return fail(FLRL_E_FORMAT, "flrl_fl_decode_static: bitsSize != ceil(outputSize/128)");
+    if (!aligned16(d_values) || !aligned16(d_out)) return fail(FLRL_E_ALIGN, "flrl_fl_decode_static: d_values and d_out must be 16-byte aligned");
+    static_assert(FLD_STATIC_WORDS * sizeof(uint64_t) >= (2 * FLD_STATIC_TILES + FLD_STATIC_TILES / 256 + 8) * sizeof(uint64_t) + 16,
+                  "the scratch holds the decoder's part of fl_workspace_bytes(FLRL_STATIC_MAX_BYTES)");
+    // the array's device address on the CURRENT device, looked up once per device
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail_cuda(e, "flrl_fl_decode_static/cudaGetDevice");
+    static std::mutex mu;
+    static void* addr[64];
+    void* ws = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (dev < 64 && addr[dev]) {
+            ws = addr[dev];
+        } else {
+            e = cudaGetSymbolAddress(&ws, g_fld_static_scratch);
+            if (e != cudaSuccess) return fail_cuda(e, "flrl_fl_decode_static/cudaGetSymbolAddress");
+            if (dev < 64) addr[dev] = ws;
+        }
+    }
+    e = fl_decode_launch(d_bits, nbits, d_values, nvalues, d_out, n, ws, s);  // memsets + two launches on `s`; allocates nothing
+    if (e != cudaSuccess) return fail_cuda(e, "flrl_fl_decode_static");
+    if (d_status) {
+        e = cudaMemcpyAsync(d_status, fl_decode_status(ws, n), sizeof(int), cudaMemcpyDeviceToDevice, s);
+        if (e != cudaSuccess) return fail_cuda(e, "flrl_fl_decode_static/status");
+    }
+    return FLRL_OK;
+}

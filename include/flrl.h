@@ -85,6 +85,20 @@ int flrl_fl_encode(const uint8_t* d_in, size_t n, uint8_t* d_bits, uint8_t* d_va
 int flrl_fl_decode(const uint8_t* d_bits, size_t nbits, const uint8_t* d_values, size_t nvalues, uint8_t* d_out, size_t n,
                    int* d_status, void* d_ws, size_t ws_bytes, flrl_stream_t stream);
 
+/*
+ * flrl_fl_decode with NO allocation anywhere on its path and no workspace argument.  It has no counterpart in the
+ * reference; it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The decoder's scratch is a file-scope static
+ * __device__ array inside the library, sized for n <= FLRL_STATIC_MAX_BYTES (1 GiB of output per call): 1.0 MiB that
+ * every GPU which loads the library holds until the process exits.  Larger n is rejected with FLRL_E_CAPACITY.  Same
+ * arguments, result and status as flrl_fl_decode; it calls neither cudaMalloc nor cudaFree nor any allocating routine.  All calls on
+ * one GPU share the scratch (what must start at zero is cleared on `stream` by every call): calls that OVERLAP on one
+ * GPU race on it — serialise them (one stream), or use flrl_fl_decode with one workspace per call in flight.
+ */
+#define FLRL_STATIC_MAX_BYTES (1ull << 30)
+int flrl_fl_decode_static(const uint8_t* d_bits, size_t nbits, const uint8_t* d_values, size_t nvalues, uint8_t* d_out, size_t n,
+                          int* d_status, flrl_stream_t stream);
+
 /* ------------------------------------------------------------------ DEVICE layer: RL ---- */
 
 size_t flrl_rl_workspace_bytes(size_t n);
