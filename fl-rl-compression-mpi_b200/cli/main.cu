@@ -33,6 +33,17 @@ int gpuCount(Method m)
     return e ? atoi(e) : 1;
 }
 
+// contexts, kernel modules and (several GPUs) NCCL communicators, timed apart from the codec: in a short-lived process
+// this set-up, not the codec, is most of a multi-GPU run on a small file
+void prepareGpus(Method m)
+{
+    Timers::CpuTimer t;
+    t.start();
+    check(flrl_prepare(gpuCount(m)));
+    t.end();
+    t.printResult("GPU set-up (contexts, kernel modules, NCCL communicators)");
+}
+
 // one line pair per GPU of the last part, as the reference prints per rank (src/timers/cpu_timer_with_transfer.cu:16-40):
 // the time of that GPU's shard and the rate at which it moved its bytes over PCIe (both directions)
 void printGpuTimers(const char* what)
@@ -56,6 +67,7 @@ void compress(Method method, const char* input, const char* output)
 {
     if (usesGpu(method)) {  // file to file through bounded pinned buffers: read, GPU and write overlap (stream_io.cu)
         try {
+            prepareGpus(method);
             if (method == Method::RunLength)
                 StreamIO::compressRL(input, output, gpuCount(method));
             else
@@ -100,6 +112,7 @@ void decompress(Method method, const char* input, const char* output)
     const bool rl = method == Method::RunLength || method == Method::RunLengthCPU;
     if (usesGpu(method)) {
         try {
+            prepareGpus(method);
             if (rl)
                 StreamIO::decompressRL(input, output, gpuCount(method));
             else

@@ -1183,6 +1183,48 @@ int flrl_rl_gpu_decompress(const uint8_t* counts, const uint8_t* values, size_t 
     return FLRL_OK;
 }
 
+// One-time costs paid up front instead of inside the first codec call: CUDA context, streams and events of every GPU of
+// the call, the kernels' modules (lazy loading: a tiny encode + decode of each codec per GPU) and, for several GPUs, the
+// NCCL communicators (ncclCommInitAll: the largest item, seconds on an 8-GPU box).  Optional; the CLI calls it while its
+// reader thread fetches the first part and prints the time as its own [TIMER] line.
+int flrl_prepare(int ngpus)
+{
+    std::lock_guard<std::mutex> lk(g_host_mu);
+    DeviceGuard restore;
+    int G = 1;
+    if (int rc = device_count(ngpus, &G)) return rc;
+    int rc = for_each_gpu(G, [&](int g) -> int {
+        Dev* dp = nullptr;
+        if (begin_gpu(g, &dp)) return -1;
+        Dev& d = *dp;
+        if (d.need_pipe()) return -1;
+        const size_t n = 4096;
+        if (d.in.ensure(n + 256) || d.a.ensure(n) || d.b.ensure(n) || d.gather.ensure(n) ||
+            d.ws.ensure(std::max(fl_workspace_bytes(n), std::max(rl_encode_workspace_bytes(n), rl_decode_workspace_bytes(n)))))
+            return -1;
+        uint64_t* d_size = reinterpret_cast<uint64_t*>(d.scal.p) + 40;
+        CK(cudaMemsetAsync(d.in.p, 0, n + 256, d.s));
+        CK(fl_encode_launch(d.in.p, n, d.a.p, d.b.p, d_size, d.ws.p, d.s));           // 32 frames of width 1 -> 512 value bytes
+        CK(fl_decode_launch(d.a.p, n / 128, d.b.p, 16 * (n / 128), d.gather.p, n, d.ws.p, d.s));
+        CK(rl_encode_launch(d.in.p, n, n, 0, d.a.p, d.b.p, n, d_size, d.ws.p, d.s));  // 17 pairs
+        CK(rl_decode_launch(d.a.p, d.b.p, (n + 254) / 255, d.gather.p, n, d_size, d.ws.p, d.s));
+        CK(segment_sums_launch(d.a.p, 16, 16, reinterpret_cast<uint64_t*>(d.scal.p) + 32, d.s));
+        CK(cudaStreamSynchronize(d.s));
+        return 0;
+    });
+    if (rc) return rc;
+    if (G > 1) {
+        if ((rc = nccl_ensure(G))) return rc;
+        for (int g = 0; g < G; ++g) {
+            CK(cudaSetDevice(g_map[g]));
+            CK(cudaMemsetAsync(g_dev[g_map[g]].scal.p, 0, sizeof(uint64_t), g_dev[g_map[g]].s));
+        }
+        std::vector<uint64_t> sizes;
+        if ((rc = exchange_sizes(G, sizes))) return rc;  // the first collective sets up NCCL's channels
+    }
+    return FLRL_OK;
+}
+
 // release every cached device buffer, stream, event and pinned staging buffer, of the pipeline too
 void flrl_release(void)
 {

@@ -78,6 +78,9 @@ static constexpr int RL_NBUF = RL_NBUF_N;               // tile buffers per CTA 
 #ifndef RLE_CTAS
 #define RLE_CTAS 6
 #endif
+#ifndef RLE_FLAT
+#define RLE_FLAT 1  // skip the mask arithmetic of 32-byte pieces that only repeat the previous byte (warp vote)
+#endif
 static constexpr int RL_RING = RL_RING_PAIRS;           // staged pairs (power of two)
 static constexpr int RL_RINGB = RL_RING + 32;           // + mirror of entry 0 + over-read slack of the unaligned 16-byte reads
 static constexpr int RLE_Q = 32;                        // tiles of one CTA that may wait for their first slot
@@ -497,6 +500,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
         bar_sync(BAR_COMPUTE, RL_THREADS);
     };
 
+    [[maybe_unused]] bool try_flat = false;  // the previous tile of this CTA had few boundaries
     uint32_t k = 0;  // tiles of this CTA that have been staged
     for (;; ++k) {
         const uint32_t kb = k & 1u, buf_i = k % RL_NBUF, fpar = (k / RL_NBUF) & 1u;
@@ -537,6 +541,19 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
                 const uint4 a = *reinterpret_cast<const uint4*>(rowp + (((chunk0 + 2u * g) ^ sw) << 4));
                 const uint4 c = *reinterpret_cast<const uint4*>(rowp + (((chunk0 + 2u * g + 1u) ^ sw) << 4));
                 const uint32_t w[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+#if RLE_FLAT
+                // long runs: most 32-byte pieces only repeat the byte before them.  When that holds for the piece of
+                // every lane (a warp vote: no divergence) the mask is 0 and its ~50 instructions are skipped for 12.
+                // Tried only after a tile with few boundaries (CTA-uniform), so short-run data never pays for the test.
+                if (try_flat) {
+                    const uint32_t pb = __byte_perm(pw, 0, 0x3333);  // the previous byte in all four lanes of a word
+                    const uint32_t diff = ((a.x ^ pb) | (a.y ^ pb)) | ((a.z ^ pb) | (a.w ^ pb)) | ((c.x ^ pb) | (c.y ^ pb)) | ((c.z ^ pb) | (c.w ^ pb));
+                    if (__all_sync(0xffffffffu, diff == 0)) {
+                        M[g] = 0;
+                        continue;  // pw stays: c.w ends with the same byte
+                    }
+                }
+#endif
                 M[g] = start_mask32(w, pw);
                 pw = c.w;
             }
@@ -658,6 +675,7 @@ rl_encode_kernel(const __grid_constant__ CUtensorMap tmap, const uint8_t* __rest
             for (int i = 1; i < RL_WARPS; ++i) F_t = min(F_t, Fa[i]), L_t = max(L_t, La[i]);
             L_lastwarp = La[RL_WARPS - 1];
         }
+        try_flat = total_all < 192u;  // the same in every thread of the CTA
         RlePending& me = sh.q[k % RLE_Q];
         if (tid == 0) {
             // the tile's last 4 KiB held no run start, so d1[tile] is still empty: last run start of the tile, or "none"

@@ -181,6 +181,9 @@ void flrl_set_concat_mode(int peer);
 /* Frees the per-device caches (buffers, streams, events, pinned staging, the chunk pipeline's too) the host layer keeps
  * between calls. */
 void flrl_release(void);
+/* Optional: pays the one-time costs of the GPUs a later call with the same `ngpus` will use — contexts, streams, the
+ * kernels' modules, and for several GPUs the NCCL communicators (the largest item) — outside the first codec call. */
+int flrl_prepare(int ngpus);
 /* Chunk size of the host layer's copy / kernel / copy pipeline (default 64 MiB; 0 restores it; rounded to 4 KiB, at
  * least 64 KiB).  A test hook: outputs do not depend on it. */
 void flrl_set_pipe_chunk(size_t bytes);
