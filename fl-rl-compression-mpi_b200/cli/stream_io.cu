@@ -1,14 +1,15 @@
 // stream_io.cu — the GPU methods of the CLI, file to file, through bounded pinned buffers.
 //
 // Replaces the reference's whole-file malloc + fread, codec call, whole-file fwrite
-// (/root/reference/src/file_io.cu:73-115, :194-280; src/main.cu:72-129): the file is cut into PARTS (256 MiB, 128 MiB
-// per GPU when there are several); a reader thread fills part j+1 (parallel preads into pinned memory) while the host
+// (/root/reference/src/file_io.cu:73-115, :194-280; src/main.cu:72-129): the file is cut into PARTS (128 MiB per GPU,
+// 256 to 512 MiB in all); a reader thread fills part j+1 (parallel preads into pinned memory) while the host
 // layer of include/flrl.h runs part j on the GPUs (its own chunk pipeline and shards inside) and a writer thread
 // writes part j-1 (parallel pwrites).  Peak host memory is three parts, not the file.  Part outputs concatenate to
 // the single-stream containers: FL parts are cut at multiples of 128 bytes; RL parts carry the run that is open at
 // their start (prev_run) and 255 bytes of look-ahead.
 #include "stream_io.cuh"
 
+#include <cuda_runtime.h>
 #include <fcntl.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -154,14 +155,17 @@ size_t part_bytes(int gpus)
         const size_t v = strtoull(e, nullptr, 10) & ~(size_t)4095;
         if (v >= 65536) return v;
     }
-    const int g = std::max(1, gpus);
-    return std::max<size_t>((size_t)256u << 20, (size_t)g * ((size_t)128u << 20));
+    // 128 MiB per GPU (two pipeline chunks per shard), at least 256 MiB, at most 512 MiB: three slots of in + out buffers
+    // are pinned up front, and pinning costs about 0.6 s per GiB — more than the codec needs for the whole file
+    const size_t g = (size_t)std::max(1, gpus);
+    return std::min<size_t>((size_t)512u << 20, std::max<size_t>((size_t)256u << 20, g * ((size_t)128u << 20)));
 }
 
 int gpus_of(int ngpus)
 {
-    if (ngpus > 0) return ngpus;
-    return 8;  // "all devices": sized for a full box; the host layer uses what is there
+    int have = 0;
+    if (cudaGetDeviceCount(&have) != cudaSuccess || have < 1) have = 1;  // the host layer reports the error itself
+    return ngpus > 0 ? std::min(ngpus, have) : have;  // 0: every GPU of the box
 }
 
 struct Acc {  // device timers of the parts, summed (max over the GPUs of a part, as the host layer reports them)
