@@ -59,8 +59,34 @@ BIG = {
     "stream64g": ("configs[4]: FL+RL on a 64 GiB sharded synthetic mixed-entropy stream", 64 * GIB),
 }
 # committed `ncu --set full` captures that hold dram__bytes_read.sum + dram__bytes_write.sum per launch (1 GiB workloads)
-NCU_FILES = {"fl": "profiles/r01_run8_fl_ncu_full.csv", "rl4": "profiles/r02_rl4_ncu_full.csv", "rl64": "profiles/r02_rl64_ncu_full.csv",
+NCU_FILES = {"fl": "profiles/r02_fl_ncu_full.csv", "rl4": "profiles/r02_rl4_ncu_full.csv", "rl64": "profiles/r02_rl64_ncu_full.csv",
              "rl4096": "profiles/r02_rl4096_ncu_full.csv"}
+
+
+def ncu_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch (bytes) of `kernel` from the committed `ncu --set full`
+    summary of `workload` (profiles/, written by tools/ncu_summary.py from a 1 GiB capture), or None."""
+    import csv
+
+    path = os.path.join(ROOT, NCU_FILES.get(workload, ""))
+    if not os.path.isfile(path):
+        return None
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        with open(path) as f:
+            rows = list(csv.reader(f))
+        hdr, units = rows[0], rows[1]
+        ir, iw, ik = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+        it = hdr.index("gpu__time_duration.sum")
+        best = None
+        for r in rows[2:]:
+            if kernel in r[ik]:
+                tot = float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]]
+                if best is None or float(r[it]) > best[0]:  # the launch that did the work (RL encode: pass 0, not the empty pass 1)
+                    best = (float(r[it]), tot)
+        return int(best[1]) if best else None
+    except (ValueError, KeyError, IndexError):
+        return None
 
 
 def peaks():
@@ -596,7 +622,8 @@ def run_ours(args):
                    "concat_in_step_ms": head["concat_in_step_ms"], "value_with_concat_to_rank0": head["value_with_concat_to_rank0"],
                    "workloads": {(r["workload"] if not big else r["workload"] + "/" + r["codec"]): {k: v for k, v in r.items() if k not in ("clocks",)} for r in results}},
         "roofline": {"bound": "hbm", "kernel": wk, "workload": wr["workload"], "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": None, "traffic_source": NCU_FILES.get(wr["workload"]),
+                     "frac": round(achieved / peak, 4), "traffic": ncu_traffic(wr["workload"], wk) if wr["bytes"] == GIB * world else None,
+                     "traffic_source": NCU_FILES.get(wr["workload"]),
                      "algorithmic_bytes": wr["algorithmic_bytes_per_gpu"], "launch_ms": wms, "peak_source": peak_src},
         "e2e": head["e2e"],
         "gpu_launches": head["gpu_launches"],
