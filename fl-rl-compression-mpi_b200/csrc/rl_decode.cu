@@ -13,7 +13,12 @@
 //     "pair that covers output byte b << sh" -> every thread owns 64-byte units aligned in the OUTPUT
 //     address space, finds the pair covering the unit's first byte by a binary search (":172-179") that the table narrows to the
 //     pairs of one block (0-1 steps instead of 12), walks the pairs of the unit and XORs value deltas
-//     into 64-bit words -> 256-bit stores (STG.256: whole 32-byte sectors).
+//     into 64-bit words -> 256-bit stores (STG.256: whole 32-byte sectors);
+//   * tiles of SHORT runs (mean count < 12): that walk diverges — every 16-byte piece costs the maximum number of pairs any
+//     lane has in its piece — so they are expanded from a bit mask of the output positions at which a pair starts (built
+//     with shared-memory atomicOr where offs[] would be): per 4 output bytes one 16-entry table look-up (PRMT selector +
+//     number of starts behind the 4 flags), one unaligned 4-byte read of the values and two PRMTs, no divergence
+//     (random bytes: 6.6 -> 2.3 ms per GiB; mean 4: 0.98 -> 0.91 ms).  tools/model_rld.py is the same arithmetic on the CPU.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -29,6 +34,9 @@ namespace flrl {
 #endif
 #ifndef RLD_CTAS
 #define RLD_CTAS 4
+#endif
+#ifndef RLD_SHORT_MEAN
+#define RLD_SHORT_MEAN 12  // tiles whose mean count is below this take the start-bit expand (0: never)
 #endif
 static constexpr int RLD_WARPS = 8;                        // compute warps
 static constexpr int RLD_THREADS = RLD_WARPS * 32;
@@ -84,6 +92,13 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
             mbar_init(&slot_free[s], RLD_WARPS);
         }
         fence_mbar_init();
+    }
+    // short-run expand: for the four start flags (b1 b2 b3 b4) behind a byte, the PRMT selector that spreads up to four
+    // consecutive values over the next 4 output bytes (byte i takes value b1 + .. + bi) | number of flags << 16
+    __shared__ uint32_t ent[16];
+    if (tid < 16) {
+        const uint32_t b1 = tid & 1u, b2 = (tid >> 1) & 1u, b3 = (tid >> 2) & 1u;
+        ent[tid] = (b1 << 4) | ((b1 + b2) << 8) | ((b1 + b2 + b3) << 12) | ((uint32_t)__popc(tid) << 16);
     }
     __syncthreads();
 
@@ -154,6 +169,8 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
     }
 
     // ================================= compute warps =======================================
+    long long pref_tile = -1;  // thread 0: tile whose scanner answer was asked for ahead of time, and the answer (or 0)
+    uint64_t g_pref = 0;
     for (uint32_t k = 0;; ++k) {
         const int s = (int)(k % RLD_SLOTS);
         mbar_wait(&full[s], (k / RLD_SLOTS) & 1u);
@@ -188,37 +205,77 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
         }
         if (lane == 31) wsum[warp] = isum;
         if (tid == 0) {
-            // the tile's first output byte: asked for by the service warp a few tiles ago
+            // the tile's first output byte: asked for by the service warp a few tiles ago; normally already fetched while
+            // the previous tile was expanded (pref_*), so that its L2 round trip is not on every warp's path to barrier A
             uint64_t g = 1ull << 63;
-            if (tile > 0)
-                while (((g = ld_relaxed_u64(inc + tile)) >> 63) == 0) __nanosleep(40);
+            if (tile > 0) {
+                g = tile == pref_tile ? g_pref : 0ull;
+                while ((g >> 63) == 0) {
+                    g = ld_relaxed_u64(inc + tile);
+                    if ((g >> 63) == 0) __nanosleep(40);
+                }
+            }
             g &= ~(1ull << 63);
             obase_s[k & 1u] = g;
             if (tile == tiles - 1) *d_out_size = g + total;
             if (g + total > out_cap) atomicExch(err, 1);
         }
         bar_sync(BAR_D, RLD_THREADS);  // A: wsum, obase; everybody is done with the previous tile's offs / tbl
+        // Short runs (mean count < RLD_SHORT_MEAN; CTA-uniform): the walk over pairs below diverges (every 16-byte piece costs
+        // the MAXIMUM number of pairs any lane has in its piece), so such tiles are expanded from a bit mask of the output
+        // positions at which a pair starts (it takes the place of offs[]): constant work per output byte, no divergence.
+        const bool short_runs = RLD_SHORT_MEAN && total < (uint32_t)RLD_SHORT_MEAN * np;  // => total < 16 * RLD_PAIRS, sh == 4
+        uint32_t* const bm = offs;  // bit x: a pair starts at output byte x of the tile (x >= 1); zero up to total + 64 and beyond
+        if (short_runs) {
+            const uint32_t nw = ((total + 64u) >> 5) + 3u;
+            for (uint32_t i = tid; i < nw; i += RLD_THREADS) bm[i] = 0u;
+            bar_sync(BAR_D, RLD_THREADS);
+        }
         uint32_t run = isum - mine;
 #pragma unroll
         for (int j = 0; j < RLD_WARPS; ++j)
             if (j < warp) run += wsum[j];
         {
             uint32_t o[16];
+            uint32_t bw = run >> 5, bits = 0;  // short runs: start bits of the word being filled
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
                 o[j] = run;
                 const uint32_t cj = (c[j >> 2] >> (8 * (j & 3))) & 0xffu;
                 for (uint32_t b = (run + (1u << sh) - 1u) >> sh; (b << sh) < run + cj; ++b) tbl[b] = (uint16_t)(tid * RLD_PER + j);
+                if (short_runs && cj && run) {  // position 0 is not marked: the pair covering byte 0 is pair 0
+                    if ((run >> 5) != bw) {
+                        if (bits) atomicOr(&bm[bw], bits);
+                        bw = run >> 5;
+                        bits = 0;
+                    }
+                    bits |= 1u << (run & 31u);
+                }
                 run += cj;
             }
-            uint4* dst = reinterpret_cast<uint4*>(offs + tid * RLD_PER);
-            dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-            dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
-            dst[2] = make_uint4(o[8], o[9], o[10], o[11]);
-            dst[3] = make_uint4(o[12], o[13], o[14], o[15]);
-            if (tid == RLD_THREADS - 1) offs[RLD_PAIRS] = run;
+            if (short_runs) {
+                if (bits) atomicOr(&bm[bw], bits);
+            } else {
+                uint4* dst = reinterpret_cast<uint4*>(offs + tid * RLD_PER);
+                dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+                dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+                dst[2] = make_uint4(o[8], o[9], o[10], o[11]);
+                dst[3] = make_uint4(o[12], o[13], o[14], o[15]);
+                if (tid == RLD_THREADS - 1) offs[RLD_PAIRS] = run;
+            }
         }
         bar_sync(BAR_D, RLD_THREADS);  // B: offs, tbl
+        if (tid == 0) {  // the next tile's first output byte, if the service warp has that tile ready and the scanner has answered
+            const int s2 = (int)((k + 1u) % RLD_SLOTS);
+            pref_tile = -1;
+            if (mbar_try_wait(&full[s2], ((k + 1u) / RLD_SLOTS) & 1u)) {
+                const long long t2 = *reinterpret_cast<const volatile long long*>(&meta[s2].tile);
+                if (t2 > 0) {
+                    pref_tile = t2;
+                    g_pref = ld_relaxed_u64(inc + t2);
+                }
+            }
+        }
 
         // ---- expand: every thread owns 64-byte units (two 32-byte stores, 32-byte aligned in the OUTPUT address space):
         // one search per unit, then a walk over the pairs of its four 16-byte pieces
@@ -227,6 +284,59 @@ rl_decode_kernel(const uint8_t* __restrict__ counts, const uint8_t* __restrict__
         const uint32_t tot = (uint32_t)lim;
         const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(out) + O) & 31u);
         const uint32_t nunits = tot ? (mis + tot + 63u) >> 6 : 0u;
+        if (short_runs) {
+            // from the pair that covers the unit's first byte on, every 4 output
+            // bytes cost one table entry (selector + number of starts), one unaligned 4-byte read of the values and two PRMTs
+            // (tools/model_rld.py is the same arithmetic on the CPU)
+            for (uint32_t q = tid; q < nunits; q += RLD_THREADS) {
+                const int p = (int)(64u * q) - (int)mis;  // tile-relative output position of the unit's first byte (< 0: first unit only)
+                // pair covering s0 = tbl[s0 >> 4] + start bits in ((s0 & ~15) + 1 .. s0].  Measured slower: a binary search over the
+                // threads' first offsets instead of tbl[] (eight dependent shared-memory reads per unit: 0.99 ms per GiB on mean 4
+                // against 0.91), and a table per 64-byte unit instead of per 16 bytes (1.01 ms).
+                const uint32_t s0 = p < 0 ? 0u : (uint32_t)p;
+                const uint32_t blk = s0 >> 4, B = blk << 4;
+                const uint32_t wB = (B & 16u) ? __funnelshift_r(bm[B >> 5], bm[(B >> 5) + 1u], 16) : bm[B >> 5];
+                uint32_t cur = (uint32_t)tbl[blk] + (uint32_t)__popc(wB & ((2u << (s0 - B)) - 2u));
+                uint32_t lo, hi;  // start bits of positions p + 1 .. p + 64
+                if (p >= 0) {
+                    const uint32_t w0 = (uint32_t)(p + 1) >> 5, sft = (uint32_t)(p + 1) & 31u;
+                    const uint32_t a = bm[w0], b = bm[w0 + 1u], c2 = bm[w0 + 2u];
+                    lo = __funnelshift_r(a, b, sft);
+                    hi = __funnelshift_r(b, c2, sft);
+                } else {
+                    const uint32_t kk = (uint32_t)(-(p + 1));  // 0 .. 30: positions p + 1 .. 0 hold no start
+                    const uint32_t a = bm[0], b = bm[1];
+                    lo = a << kk;
+                    hi = __funnelshift_l(a, b, kk);
+                }
+                uint32_t w[16];
+#pragma unroll
+                for (int wq = 0; wq < 16; ++wq) {
+                    const uint32_t e = ent[((wq < 8 ? lo : hi) >> (4 * (wq & 7))) & 15u];
+                    const uint32_t* vp = reinterpret_cast<const uint32_t*>(val + (cur & ~3u));
+                    const uint32_t v4 = __byte_perm(vp[0], vp[1], 0x3210u + 0x1111u * (cur & 3u));  // values cur .. cur + 3
+                    w[wq] = __byte_perm(v4, 0u, e & 0xffffu);
+                    cur += e >> 16;
+                }
+                uint8_t* dst = out + O + p;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    const int ps = p + 32 * half;
+                    if (ps >= 0 && (uint32_t)ps + 32u <= tot) {
+                        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 32 * half), "r"(w[8 * half]),
+                                     "r"(w[8 * half + 1]), "r"(w[8 * half + 2]), "r"(w[8 * half + 3]), "r"(w[8 * half + 4]),
+                                     "r"(w[8 * half + 5]), "r"(w[8 * half + 6]), "r"(w[8 * half + 7])
+                                     : "memory");
+                    } else {
+#pragma unroll
+                        for (int bi = 0; bi < 32; ++bi) {
+                            const int pos = ps + bi;
+                            if (pos >= 0 && (uint32_t)pos < tot) dst[32 * half + bi] = (uint8_t)(w[8 * half + (bi >> 2)] >> (8 * (bi & 3)));
+                        }
+                    }
+                }
+            }
+        } else
         for (uint32_t q = tid; q < nunits; q += RLD_THREADS) {
             const int p = (int)(64u * q) - (int)mis;  // tile-relative output position of the unit's first byte
             const uint32_t lo = p < 0 ? 0u : (uint32_t)p;
