@@ -234,6 +234,8 @@ lib.flrl_free.argtypes = [_vp]
 lib.flrl_last_timing.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
 lib.flrl_set_concat_mode.argtypes = [C.c_int]
 lib.flrl_set_pipe_chunk.argtypes = [_sz]
+lib.flrl_prepare.restype = C.c_int
+lib.flrl_prepare.argtypes = [C.c_int]
 lib.flrl_last_gpu_count.restype = C.c_int
 lib.flrl_last_timing_gpu.restype = C.c_int
 lib.flrl_last_timing_gpu.argtypes = [C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]

@@ -294,7 +294,7 @@ void compressRL(const char* input, const char* output, int ngpus)
 {
     const double t0 = now_ms();
     Fd in(input, O_RDONLY, "[FileIO] Cannot open file");
-    Fd out(output, O_WRONLY | O_CREAT | O_TRUNC, "[FileIO] Cannot open file");
+    Fd out(output, O_RDWR | O_CREAT | O_TRUNC, "[FileIO] Cannot open file");  // read back once: the parked values
     const size_t n = in.size();
     const size_t S = part_bytes(gpus_of(ngpus));
     const long parts = (long)((n + S - 1) / S);
@@ -310,9 +310,10 @@ void compressRL(const char* input, const char* output, int ngpus)
     // the run that is open at the end of the part read last: its byte and its length (carried over whole parts)
     int tail_byte = -1;
     uint64_t tail_run = 0;
-    // the container puts all counts before all values, and the pair count is known only at the end: the values wait in
-    // host memory (at most one byte per pair) and are written behind the counts when the last part is done
-    std::vector<uint8_t> all_values;
+    // the container puts all counts before all values, and the pair count P is known only at the end: the values are parked in
+    // the output file itself, behind the place of the last possible count (P <= n), and moved down to 16 + P when the last
+    // part is done (P bytes through one pinned buffer; little for the inputs RL is meant for).  Host memory stays O(parts).
+    const size_t park = 16 + n;
     Ring ring;
     Acc acc;
     auto len = [&](long j) { return std::min(S, n - (size_t)j * S); };
@@ -336,11 +337,19 @@ void compressRL(const char* input, const char* output, int ngpus)
         },
         [&](long j, int k) {
             io_all(out.fd, dc[k]->p, np[j], 16 + poff[j], true);
-            all_values.insert(all_values.end(), dv[k]->p, dv[k]->p + np[j]);
+            io_all(out.fd, dv[k]->p, np[j], park + poff[j], true);
         });
     const size_t P = poff[std::max(0L, parts)];
     const double tw = now_ms();
-    io_all(out.fd, all_values.data(), P, 16 + P, true);
+    if (P && parts > 0) {  // values: from park .. park + P down to 16 + P .. 16 + 2 P, ascending (source is always ahead of the target)
+        uint8_t* buf = dv[0]->p;
+        for (size_t o = 0; o < P; o += cap) {
+            const size_t m = std::min(cap, P - o);
+            io_all(out.fd, buf, m, park + o, false);
+            io_all(out.fd, buf, m, 16 + P + o, true);
+        }
+    }
+    if (ftruncate(out.fd, (off_t)(16 + 2 * P)) != 0) throw std::runtime_error("[FileIO] Cannot write to file");
     const uint64_t hdr[2] = {n, P};
     io_all(out.fd, reinterpret_cast<uint8_t*>(const_cast<uint64_t*>(hdr)), sizeof hdr, 0, true);
     ring.busy_ms[2] += now_ms() - tw;

@@ -132,6 +132,7 @@ def test_host_release_and_reuse(oracle, flrl):
         hc.load_input(data)
         hc.compress()
         flrl.lib.flrl_release()
+        assert flrl.lib.flrl_prepare(1) == 0  # optional: contexts, kernel modules (and NCCL for several GPUs) up front
         hc.compress()
         hc.decompress()
         assert hc.check_round_trip()
