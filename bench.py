@@ -331,14 +331,17 @@ class Work:
 
     def step(self, exchange=None, events=None):
         """compress the shard, [exchange the sizes], decompress it; pieces back to back."""
-        self.total_size.zero_()
+        single = len(self.cuts) == 1  # one launch per shard: the kernel's own size word is the shard's size (no extra launches)
+        if not single:
+            self.total_size.zero_()
         for i in range(len(self.cuts)):
             if events:
                 events[i][0].record()
             self._encode(i)
             if events:
                 events[i][1].record()
-            self.total_size += self.enc.size
+            if not single:
+                self.total_size += self.enc.size
             if exchange and i == len(self.cuts) - 1:
                 exchange()
             if events:
@@ -346,6 +349,9 @@ class Work:
             self._decode(i)
             if events:
                 events[i][3].record()
+
+    def size_tensor(self):
+        return self.enc.size if len(self.cuts) == 1 else self.total_size
 
     def payload(self):
         return self.enc.values if self.kind == "fl" else self.enc.counts
@@ -425,7 +431,7 @@ def measure(args, torch, dist, flrl, sharding, workload, kind, rank, local, worl
     def exchange():
         """N > 1, inside every timed step: the ONLY exchange of the path — all-gather the per-shard compressed sizes
         (one u64 per GPU, NCCL) and turn them into output offsets by an exclusive scan, on the device, no host sync."""
-        sharding.exchange_sizes(dist, work.total_size, sizes, offsets)  # the logic tests/test_sharding_gloo.py runs over gloo
+        sharding.exchange_sizes(dist, work.size_tensor(), sizes, offsets)  # the logic tests/test_sharding_gloo.py runs over gloo
 
     ex = exchange if world > 1 else None
     ev = lambda: torch.cuda.Event(enable_timing=True)
