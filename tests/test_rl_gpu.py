@@ -144,3 +144,27 @@ def test_rl_full_size_properties(mean, oracle, flrl):
     assert counts.numel() == c_ref.size
     assert np.array_equal(counts.cpu().numpy(), c_ref)
     assert np.array_equal(values.cpu().numpy(), v_ref)
+
+
+@pytest.mark.parametrize("mean", [1, 2])
+def test_rl_dense_data_at_scale(mean, oracle, flrl):
+    """Dense data (random bytes, mean run 2) at 256 MiB: every 16 KiB tile has more pair boundaries than the encoder's ring
+    of staged pairs holds, so all of them go through its second pass, and the decoder takes its short-run (start-bit)
+    expand everywhere.  Every pair is compared with the oracle."""
+    import torch
+
+    import bench
+
+    n = 1 << 28
+    d_in = torch.randint(0, 256, (n,), dtype=torch.uint8, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5)) \
+        if mean == 1 else bench.gen_rl_device(torch, n, 2)
+    enc = flrl.RLEncoder(n)
+    enc.launch(d_in)
+    counts, values = enc.result()
+    c_ref, v_ref = oracle.rl_compress(d_in.cpu().numpy())
+    assert counts.numel() == c_ref.size
+    assert np.array_equal(counts.cpu().numpy(), c_ref)
+    assert np.array_equal(values.cpu().numpy(), v_ref)
+    dec = flrl.RLDecoder(n, counts.numel())
+    dec.launch(counts, values)
+    assert torch.equal(dec.result(), d_in)
